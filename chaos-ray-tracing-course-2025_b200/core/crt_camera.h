@@ -1,0 +1,3 @@
+#pragma once
+// API-compatibility shim: in the reference this is src/core/crt_camera.h; here the scene types live together.
+#include "crt_scene.h"

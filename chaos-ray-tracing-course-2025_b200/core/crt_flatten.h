@@ -1,0 +1,30 @@
+#pragma once
+// Scene -> 16-byte-aligned POD arrays (include/crt_cuda.h: crt_flat_scene).  This is the "scene upload and tree
+// flattening" subsystem: it has no counterpart in the reference, whose renderer walks std::vector<Node> with
+// per-node std::vector<Triangle> (src/core/crt_acceleration_tree.h:15-26).
+#include <vector>
+
+#include "../../include/crt_cuda.h"
+#include "crt_scene.h"
+
+namespace crt {
+
+struct FlatScene {
+    std::vector<crt_float4> tri_verts;
+    std::vector<int32_t> tri_meta;
+    std::vector<crt_float4> vert_normal;
+    std::vector<float> vert_uv;
+    std::vector<crt_box_node> box_nodes;
+    std::vector<crt_kd_node> kd_nodes;
+    std::vector<uint32_t> refs;
+    std::vector<crt_float4> lights;
+    std::vector<crt_material> materials;
+    std::vector<crt_texture> textures;
+    std::vector<crt_float4> texels;
+    crt_flat_scene view{}; // pointers into the vectors above
+};
+
+crt_camera flatten_camera(const Camera &camera);
+void flatten_scene(const Scene &scene, FlatScene &out);
+
+} // namespace crt

@@ -1,0 +1,487 @@
+// C-ABI implementation (include/crt_cuda.h, crt_cuda_* group): device context, scene upload, kernel launches.
+// There is no CPU fallback anywhere in this file: without a CUDA device every entry point fails loudly.
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "crt_kernels.cuh"
+#include "crt_wavefront.cuh"
+
+using namespace crtdev;
+
+struct crt_cuda_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::string error;
+
+    char *d_arena = nullptr; // every scene array, one allocation
+    size_t d_arena_cap = 0;
+    char *h_arena = nullptr; // pinned staging of the same layout
+    size_t h_arena_cap = 0;
+    DScene scene{};
+    bool have_scene = false;
+
+    float *d_rgb = nullptr;
+    uint8_t *d_rgb8 = nullptr;
+    size_t fb_pixels = 0;
+    Counters *d_counters = nullptr;
+    Counters *h_counters = nullptr; // pinned
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    int last_width = 0, last_rows = 0, last_launches = 0;
+    bool last_stats = false;
+
+    WavefrontState wf; // ray queues of the wavefront pipeline (crt_wavefront.cuh)
+
+    char *d_text = nullptr; // PPM text
+    size_t d_text_cap = 0;
+    unsigned long long *d_scan = nullptr;
+    size_t d_scan_cap = 0;
+};
+
+namespace {
+
+thread_local std::string g_create_error;
+
+#define CRT_CK(ctx, call)                                                                                     \
+    do {                                                                                                      \
+        cudaError_t e_ = (call);                                                                              \
+        if (e_ != cudaSuccess) {                                                                              \
+            (ctx)->error = std::string(#call) + ": " + cudaGetErrorString(e_);                                \
+            return CRT_ERR_CUDA;                                                                              \
+        }                                                                                                     \
+    } while (0)
+
+int fail(crt_cuda_ctx *ctx, int code, const char *what) {
+    ctx->error = what;
+    return code;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int owned_rows(const crt_render_params &p, int height) {
+    if (p.world <= 1)
+        return height;
+    const int band = p.band_rows > 0 ? p.band_rows : 8;
+    const int bands = (height + band - 1) / band;
+    int rows = 0;
+    for (int b = p.rank; b < bands; b += p.world)
+        rows += (b == bands - 1) ? height - b * band : band;
+    return rows;
+}
+
+DParams device_params(const crt_render_params &p, int height) {
+    DParams d{};
+    d.max_ray_depth = p.max_ray_depth > uint32_t(kMaxDepthCap) ? uint32_t(kMaxDepthCap) : p.max_ray_depth;
+    d.gi_rays = p.diffuse_reflection_ray_count;
+    d.shadow_bias = p.shadow_bias;
+    d.reflection_bias = p.reflection_bias;
+    d.diffuse_reflection_bias = p.diffuse_reflection_bias;
+    d.refraction_bias = p.refraction_bias;
+    d.shadows = p.shadows;
+    d.rank = p.rank;
+    d.world = p.world;
+    d.band_rows = p.band_rows > 0 ? p.band_rows : 8;
+    d.rows = owned_rows(p, height);
+    return d;
+}
+
+int ensure_framebuffer(crt_cuda_ctx *ctx, size_t pixels) {
+    if (pixels <= ctx->fb_pixels)
+        return CRT_OK;
+    if (ctx->d_rgb)
+        cudaFree(ctx->d_rgb);
+    if (ctx->d_rgb8)
+        cudaFree(ctx->d_rgb8);
+    ctx->d_rgb = nullptr, ctx->d_rgb8 = nullptr, ctx->fb_pixels = 0;
+    CRT_CK(ctx, cudaMalloc(&ctx->d_rgb, pixels * 3 * sizeof(float)));
+    CRT_CK(ctx, cudaMalloc(&ctx->d_rgb8, pixels * 3));
+    ctx->fb_pixels = pixels;
+    return CRT_OK;
+}
+
+void fill_stats(const crt_cuda_ctx *ctx, crt_render_stats *stats, float ms) {
+    if (!stats)
+        return;
+    std::memset(stats, 0, sizeof *stats);
+    stats->gpu_ms = ms;
+    stats->kernel_launches = ctx->last_launches;
+    stats->rows_rendered = ctx->last_rows;
+    if (ctx->last_stats) {
+        const Counters &c = *ctx->h_counters;
+        stats->rays = c.rays;
+        stats->shadow_rays = c.shadow_rays;
+        stats->node_tests = c.node_tests;
+        stats->tri_tests = c.tri_tests;
+        for (int i = 0; i < 16; ++i)
+            stats->rays_by_depth[i] = c.rays_by_depth[i];
+    }
+}
+
+template <int TRAV>
+void launch_mega(crt_cuda_ctx *ctx, const DParams &dp, bool stats, dim3 grid) {
+    if (stats)
+        k_render_mega<TRAV, true><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+    else
+        k_render_mega<TRAV, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+}
+
+// enqueue one frame on ctx->stream, bracketed by the timing events
+int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
+    if (!ctx->have_scene)
+        return fail(ctx, CRT_ERR_INVALID, "no scene uploaded");
+    if (!params)
+        return fail(ctx, CRT_ERR_INVALID, "params is NULL");
+    if (params->traversal != CRT_TRAVERSAL_LITERAL && params->traversal != CRT_TRAVERSAL_KD)
+        return fail(ctx, CRT_ERR_INVALID, "render supports CRT_TRAVERSAL_LITERAL or CRT_TRAVERSAL_KD (brute force is a primary-hit checker only)");
+    if (params->world > 1 && (params->rank < 0 || params->rank >= params->world))
+        return fail(ctx, CRT_ERR_INVALID, "rank outside [0, world)");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    const int W = ctx->scene.cam.width, H = ctx->scene.cam.height;
+    const DParams dp = device_params(*params, H);
+    if (int rc = ensure_framebuffer(ctx, size_t(W) * size_t(dp.rows > 0 ? dp.rows : 1)))
+        return rc;
+    const bool stats = params->collect_stats != 0;
+    ctx->last_stats = stats;
+    ctx->last_width = W;
+    ctx->last_rows = dp.rows;
+    ctx->last_launches = 0;
+    if (stats)
+        CRT_CK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), ctx->stream));
+    CRT_CK(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
+    if (dp.rows > 0 && W > 0) {
+        int pipeline = params->pipeline;
+        const bool needs_mega = (ctx->scene.gi_on && dp.gi_rays > 0) || params->shadows;
+        if (pipeline == CRT_PIPELINE_AUTO)
+            pipeline = (needs_mega || !kWavefrontReady) ? CRT_PIPELINE_MEGAKERNEL : CRT_PIPELINE_WAVEFRONT;
+        if (pipeline == CRT_PIPELINE_WAVEFRONT && needs_mega)
+            return fail(ctx, CRT_ERR_INVALID, "the wavefront pipeline does not handle GI or shadow rays; use CRT_PIPELINE_MEGAKERNEL");
+        if (pipeline == CRT_PIPELINE_WAVEFRONT) {
+            int launches = 0;
+            cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, ctx->stream,
+                                             &launches);
+            if (e != cudaSuccess)
+                return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
+            ctx->last_launches = launches;
+        } else {
+            const dim3 grid((W + kTileW - 1) / kTileW, (dp.rows + kTileH - 1) / kTileH);
+            if (params->traversal == CRT_TRAVERSAL_LITERAL)
+                launch_mega<CRT_TRAVERSAL_LITERAL>(ctx, dp, stats, grid);
+            else
+                launch_mega<CRT_TRAVERSAL_KD>(ctx, dp, stats, grid);
+            ctx->last_launches = 1;
+        }
+        CRT_CK(ctx, cudaGetLastError());
+    }
+    CRT_CK(ctx, cudaEventRecord(ctx->ev_end, ctx->stream));
+    if (stats)
+        CRT_CK(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, ctx->stream));
+    return CRT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+void crt_render_params_default(crt_render_params *p) {
+    if (!p)
+        return;
+    std::memset(p, 0, sizeof *p);
+    p->max_ray_depth = 3;                // DEFAULT_MAX_RAY_DEPTH, src/core/crt_renderer.h:10
+    p->diffuse_reflection_ray_count = 4; // :11
+    p->shadow_bias = p->reflection_bias = p->diffuse_reflection_bias = p->refraction_bias = 1e-2f; // :13-16
+    p->traversal = CRT_TRAVERSAL_KD;
+    p->pipeline = CRT_PIPELINE_AUTO;
+    p->world = 1;
+    p->band_rows = 8;
+}
+
+int crt_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+        return 0;
+    return n;
+}
+
+int crt_cuda_create(int device, crt_cuda_ctx **out) {
+    if (!out)
+        return CRT_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        std::fprintf(stderr, "crt_cuda_create: no CUDA device (%s); this renderer has no CPU fallback\n",
+                     e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return CRT_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= n)
+        return CRT_ERR_INVALID;
+    crt_cuda_ctx *ctx = new crt_cuda_ctx;
+    ctx->device = device;
+    bool ok = cudaSetDevice(device) == cudaSuccess && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreate(&ctx->ev_begin) == cudaSuccess && cudaEventCreate(&ctx->ev_end) == cudaSuccess &&
+              cudaMalloc(&ctx->d_counters, sizeof(Counters)) == cudaSuccess &&
+              cudaHostAlloc(&ctx->h_counters, sizeof(Counters), cudaHostAllocDefault) == cudaSuccess;
+    if (!ok) {
+        std::fprintf(stderr, "crt_cuda_create: %s\n", cudaGetErrorString(cudaGetLastError()));
+        crt_cuda_destroy(ctx);
+        return CRT_ERR_CUDA;
+    }
+    std::memset(ctx->h_counters, 0, sizeof(Counters));
+    ctx->stream = ctx->own_stream;
+    *out = ctx;
+    return CRT_OK;
+}
+
+void crt_cuda_destroy(crt_cuda_ctx *ctx) {
+    if (!ctx)
+        return;
+    cudaSetDevice(ctx->device);
+    if (ctx->own_stream)
+        cudaStreamSynchronize(ctx->own_stream);
+    wavefront_free(ctx->wf);
+    cudaFree(ctx->d_arena);
+    cudaFreeHost(ctx->h_arena);
+    cudaFree(ctx->d_rgb);
+    cudaFree(ctx->d_rgb8);
+    cudaFree(ctx->d_counters);
+    cudaFreeHost(ctx->h_counters);
+    cudaFree(ctx->d_text);
+    cudaFree(ctx->d_scan);
+    if (ctx->ev_begin)
+        cudaEventDestroy(ctx->ev_begin);
+    if (ctx->ev_end)
+        cudaEventDestroy(ctx->ev_end);
+    if (ctx->own_stream)
+        cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+}
+
+const char *crt_cuda_last_error(const crt_cuda_ctx *ctx) { return ctx ? ctx->error.c_str() : "null context"; }
+
+int crt_cuda_set_stream(crt_cuda_ctx *ctx, void *stream) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    ctx->stream = stream ? static_cast<cudaStream_t>(stream) : ctx->own_stream;
+    return CRT_OK;
+}
+
+int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!s)
+        return fail(ctx, CRT_ERR_INVALID, "scene is NULL");
+    if (s->n_nodes < 1 || !s->box_nodes || !s->kd_nodes)
+        return fail(ctx, CRT_ERR_INVALID, "scene has no acceleration tree");
+    if (s->max_depth + 2 > kStack)
+        return fail(ctx, CRT_ERR_INVALID, "acceleration tree deeper than the traversal stack");
+    if (s->camera.width < 0 || s->camera.height < 0)
+        return fail(ctx, CRT_ERR_INVALID, "negative image size");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+
+    struct Part {
+        const void *src;
+        size_t bytes;
+        size_t offset;
+    };
+    Part parts[11] = {
+        { s->tri_verts, size_t(s->n_triangles) * 3 * sizeof(crt_float4), 0 },
+        { s->tri_meta, size_t(s->n_triangles) * 4 * sizeof(int32_t), 0 },
+        { s->vert_normal, size_t(s->n_vertices) * sizeof(crt_float4), 0 },
+        { s->vert_uv, size_t(s->n_vertices) * 2 * sizeof(float), 0 },
+        { s->box_nodes, size_t(s->n_nodes) * sizeof(crt_box_node), 0 },
+        { s->kd_nodes, size_t(s->n_nodes) * sizeof(crt_kd_node), 0 },
+        { s->refs, size_t(s->n_refs) * sizeof(uint32_t), 0 },
+        { s->lights, size_t(s->n_lights) * sizeof(crt_float4), 0 },
+        { s->materials, size_t(s->n_materials) * sizeof(crt_material), 0 },
+        { s->textures, size_t(s->n_textures) * sizeof(crt_texture), 0 },
+        { s->texels, size_t(s->n_texels) * sizeof(crt_float4), 0 },
+    };
+    size_t total = 0;
+    for (Part &p : parts) {
+        if (p.bytes && !p.src)
+            return fail(ctx, CRT_ERR_INVALID, "scene array pointer is NULL");
+        p.offset = total;
+        total += align_up(p.bytes ? p.bytes : 16, 256);
+    }
+    if (total > ctx->d_arena_cap) {
+        cudaFree(ctx->d_arena);
+        ctx->d_arena = nullptr, ctx->d_arena_cap = 0;
+        CRT_CK(ctx, cudaMalloc(&ctx->d_arena, total));
+        ctx->d_arena_cap = total;
+    }
+    if (total > ctx->h_arena_cap) {
+        cudaFreeHost(ctx->h_arena);
+        ctx->h_arena = nullptr, ctx->h_arena_cap = 0;
+        CRT_CK(ctx, cudaHostAlloc(&ctx->h_arena, total, cudaHostAllocDefault));
+        ctx->h_arena_cap = total;
+    }
+    // make sure an earlier frame is not still reading the arena we are about to overwrite
+    CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    for (const Part &p : parts)
+        if (p.bytes)
+            std::memcpy(ctx->h_arena + p.offset, p.src, p.bytes);
+    CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena, ctx->h_arena, total, cudaMemcpyHostToDevice, ctx->stream));
+
+    DScene &d = ctx->scene;
+    d = DScene{};
+    d.cam = s->camera;
+    std::memcpy(d.bg, s->background, sizeof d.bg);
+    d.gi_on = s->gi_on, d.reflections_on = s->reflections_on, d.refractions_on = s->refractions_on;
+    std::memcpy(d.root_min, s->root_min, sizeof d.root_min);
+    std::memcpy(d.root_max, s->root_max, sizeof d.root_max);
+    d.n_triangles = s->n_triangles, d.n_nodes = s->n_nodes, d.n_lights = s->n_lights, d.n_materials = s->n_materials, d.n_textures = s->n_textures;
+    d.tri_verts = reinterpret_cast<const float4 *>(ctx->d_arena + parts[0].offset);
+    d.tri_meta = reinterpret_cast<const int4 *>(ctx->d_arena + parts[1].offset);
+    d.vert_normal = reinterpret_cast<const float4 *>(ctx->d_arena + parts[2].offset);
+    d.vert_uv = reinterpret_cast<const float2 *>(ctx->d_arena + parts[3].offset);
+    d.box_nodes = reinterpret_cast<const float4 *>(ctx->d_arena + parts[4].offset);
+    d.kd_nodes = reinterpret_cast<const int4 *>(ctx->d_arena + parts[5].offset);
+    d.refs = reinterpret_cast<const uint32_t *>(ctx->d_arena + parts[6].offset);
+    d.lights = reinterpret_cast<const float4 *>(ctx->d_arena + parts[7].offset);
+    d.materials = reinterpret_cast<const int4 *>(ctx->d_arena + parts[8].offset);
+    d.textures = reinterpret_cast<const float4 *>(ctx->d_arena + parts[9].offset);
+    d.texels = reinterpret_cast<const float4 *>(ctx->d_arena + parts[10].offset);
+    ctx->have_scene = true;
+    return CRT_OK;
+}
+
+int crt_cuda_set_camera(crt_cuda_ctx *ctx, const crt_camera *camera) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!camera || !ctx->have_scene)
+        return fail(ctx, CRT_ERR_INVALID, "set_camera needs an uploaded scene and a camera");
+    // the camera block travels as a kernel parameter (__grid_constant__), i.e. with the launch itself
+    ctx->scene.cam = *camera;
+    return CRT_OK;
+}
+
+int crt_cuda_render_device(crt_cuda_ctx *ctx, const crt_render_params *params, crt_render_stats *stats) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (int rc = enqueue_frame(ctx, params))
+        return rc;
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        stats->kernel_launches = ctx->last_launches;
+        stats->rows_rendered = ctx->last_rows;
+    }
+    return CRT_OK;
+}
+
+int crt_cuda_synchronize(crt_cuda_ctx *ctx, crt_render_stats *stats) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0.0f;
+    if (stats && ctx->last_width)
+        cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end);
+    fill_stats(ctx, stats, ms);
+    return CRT_OK;
+}
+
+int crt_cuda_render(crt_cuda_ctx *ctx, const crt_render_params *params, float *rgb_out, uint8_t *rgb8_out, crt_render_stats *stats) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (int rc = enqueue_frame(ctx, params))
+        return rc;
+    const size_t pixels = size_t(ctx->last_width) * size_t(ctx->last_rows);
+    if (rgb_out && pixels)
+        CRT_CK(ctx, cudaMemcpyAsync(rgb_out, ctx->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rgb8_out && pixels)
+        CRT_CK(ctx, cudaMemcpyAsync(rgb8_out, ctx->d_rgb8, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    return crt_cuda_synchronize(ctx, stats);
+}
+
+int crt_cuda_device_framebuffer(crt_cuda_ctx *ctx, void **rgb_dev, void **rgb8_dev, int *width, int *rows) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (rgb_dev)
+        *rgb_dev = ctx->d_rgb;
+    if (rgb8_dev)
+        *rgb8_dev = ctx->d_rgb8;
+    if (width)
+        *width = ctx->last_width;
+    if (rows)
+        *rows = ctx->last_rows;
+    return CRT_OK;
+}
+
+int crt_cuda_primary_rays(crt_cuda_ctx *ctx, float *rays_out) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!ctx->have_scene || !rays_out)
+        return fail(ctx, CRT_ERR_INVALID, "primary_rays needs an uploaded scene and an output buffer");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    const int W = ctx->scene.cam.width, H = ctx->scene.cam.height;
+    const size_t n = size_t(W) * H;
+    if (!n)
+        return CRT_OK;
+    float *d = nullptr;
+    CRT_CK(ctx, cudaMalloc(&d, n * 6 * sizeof(float)));
+    k_primary_rays<<<dim3((W + kTileW - 1) / kTileW, (H + kTileH - 1) / kTileH), kBlock, 0, ctx->stream>>>(ctx->scene, d);
+    cudaError_t e = cudaMemcpyAsync(rays_out, d, n * 6 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    CRT_CK(ctx, e);
+    return CRT_OK;
+}
+
+int crt_cuda_primary_hits(crt_cuda_ctx *ctx, int traversal, int32_t *tri_id, float *t, int32_t *node_tests, int32_t *tri_tests, crt_render_stats *stats) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!ctx->have_scene)
+        return fail(ctx, CRT_ERR_INVALID, "no scene uploaded");
+    if (traversal < CRT_TRAVERSAL_LITERAL || traversal > CRT_TRAVERSAL_BRUTE)
+        return fail(ctx, CRT_ERR_INVALID, "unknown traversal");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    const int W = ctx->scene.cam.width, H = ctx->scene.cam.height;
+    const size_t n = size_t(W) * H;
+    if (!n)
+        return CRT_OK;
+    int32_t *d_tri = nullptr, *d_nn = nullptr, *d_nt = nullptr;
+    float *d_t = nullptr;
+    cudaError_t e = cudaMalloc(&d_tri, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_t, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_nn, n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_nt, n * 4);
+    if (e == cudaSuccess) e = cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), ctx->stream);
+    if (e == cudaSuccess) {
+        const dim3 grid((W + kTileW - 1) / kTileW, (H + kTileH - 1) / kTileH);
+        cudaEventRecord(ctx->ev_begin, ctx->stream);
+        if (traversal == CRT_TRAVERSAL_LITERAL)
+            k_primary_hits<CRT_TRAVERSAL_LITERAL><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, d_tri, d_t, d_nn, d_nt, ctx->d_counters);
+        else if (traversal == CRT_TRAVERSAL_KD)
+            k_primary_hits<CRT_TRAVERSAL_KD><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, d_tri, d_t, d_nn, d_nt, ctx->d_counters);
+        else
+            k_primary_hits<CRT_TRAVERSAL_BRUTE><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, d_tri, d_t, d_nn, d_nt, ctx->d_counters);
+        cudaEventRecord(ctx->ev_end, ctx->stream);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess && tri_id) e = cudaMemcpyAsync(tri_id, d_tri, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && t) e = cudaMemcpyAsync(t, d_t, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && node_tests) e = cudaMemcpyAsync(node_tests, d_nn, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && tri_tests) e = cudaMemcpyAsync(tri_tests, d_nt, n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_tri), cudaFree(d_t), cudaFree(d_nn), cudaFree(d_nt);
+    CRT_CK(ctx, e);
+    ctx->last_stats = true;
+    ctx->last_launches = 1;
+    ctx->last_rows = H;
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end);
+    fill_stats(ctx, stats, ms);
+    return CRT_OK;
+}
+
+int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size_t *length) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    return fail(ctx, CRT_ERR_INVALID, "crt_cuda_encode_ppm: not built yet");
+}
+
+} // extern "C"
