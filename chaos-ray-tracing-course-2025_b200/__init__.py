@@ -177,6 +177,7 @@ class Scene:
         rc = lib.crt_scene_flatten(self._h, C.byref(flat))
         if rc != CRT_OK:
             raise CrtError(f"crt_scene_flatten -> {rc}")
+        flat._owner = self  # the arrays live in the scene handle: keep it alive as long as the view
         self._flat = flat
         return flat
 

@@ -321,3 +321,46 @@ def port_primary_rays(flat) -> np.ndarray:
     rays = np.zeros((flat.camera.height, flat.camera.width, 6), np.float32)
     assert lib.crt_oracle_primary_rays(C.byref(flat), _p(rays)) == 0
     return rays
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# canonical byte strings of a loaded scene, computable from either side (for the committed digests)
+# ---------------------------------------------------------------------------------------------------------------
+def canonical_scene_bytes_from_dump(dump) -> dict:
+    nodes, refs = dump["nodes"], dump["refs"]
+    leaf = nodes["count"] > 0
+    links = np.stack([np.where(leaf, -nodes["first"] - 2, nodes["c0"]), np.where(leaf, nodes["count"], nodes["c1"])], axis=1).astype(np.int32)
+    return {
+        "vertex_normals": np.ascontiguousarray(dump["vertices"][:, 3:6]).tobytes(),
+        "vertex_uvs": np.ascontiguousarray(dump["vertices"][:, 6:8]).tobytes(),
+        "node_boxes": np.ascontiguousarray(np.concatenate([nodes["min"], nodes["max"]], axis=1)).tobytes(),
+        "node_links": links.tobytes(),
+        "ref_triangles": np.ascontiguousarray(refs["tri"].astype(np.int32)).tobytes(),
+        "ref_vertices": np.ascontiguousarray(refs["v"].astype(np.int32)).tobytes(),
+        "ref_normals": np.ascontiguousarray(refs["normal"]).tobytes(),
+        "lights": np.ascontiguousarray(dump["lights"]).tobytes(),
+    }
+
+
+def canonical_scene_bytes_from_flat(flat) -> dict:
+    a = flat.arrays()
+    box = a["box_nodes"]
+    tri = (a["refs"] & 0x7FFFFFFF).astype(np.int64)
+    return {
+        "vertex_normals": np.ascontiguousarray(a["vert_normal"][:, :3]).tobytes(),
+        "vertex_uvs": np.ascontiguousarray(a["vert_uv"]).tobytes(),
+        "node_boxes": np.ascontiguousarray(np.concatenate([box[:, 0:3], box[:, 4:7]], axis=1)).tobytes(),
+        "node_links": np.ascontiguousarray(np.stack([box[:, 3], box[:, 7]], axis=1).astype(np.int32)).tobytes(),
+        "ref_triangles": tri.astype(np.int32).tobytes(),
+        "ref_vertices": np.ascontiguousarray(a["tri_meta"][tri][:, :3].astype(np.int32)).tobytes(),
+        "ref_normals": np.ascontiguousarray(a["tri_verts"][tri][:, :, 3]).tobytes(),
+        "lights": np.ascontiguousarray(np.concatenate([a["lights"][:, 3:4], a["lights"][:, :3]], axis=1)).tobytes(),
+    }
+
+
+def golden_path(rel: str) -> str:
+    return os.path.join(ROOT, "tests", "golden", rel.replace("/", "__").replace(".crtscene", "") + ".npz")
+
+
+def golden_size(rel: str):
+    return (48, 48) if rel.startswith("15-01-conclusion/scene2") else (96, 54)

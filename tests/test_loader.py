@@ -1,0 +1,161 @@
+"""Host logic: the .crtscene loader, the tree builder and the flattener against the reference (live when oracle/_ref is
+built, and against the committed digests generated from it)."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_tools as otools
+
+DIGESTS = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "scene_digests.json")))
+needs_scenes = pytest.mark.skipif(not (otools.have_reference_build() or os.path.isdir("/root/reference/src")),
+                                  reason="scene fixtures live in oracle/_ref/scenes (built where /root/reference is mounted)")
+
+
+@needs_scenes
+@pytest.mark.parametrize("rel", otools.LOADABLE_SCENES)
+def test_flattened_scene_matches_reference_digests(crt, ot, rel):
+    flat_owner = crt.Scene.load_file(ot.scene_file(rel))
+    flat = flat_owner.flatten()
+    got = {k: hashlib.sha256(v).hexdigest() for k, v in ot.canonical_scene_bytes_from_flat(flat).items()}
+    assert got == DIGESTS[rel]
+
+
+@needs_scenes
+@pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "15-01-conclusion/scene2.crtscene", "12-01-textures/scene4.crtscene",
+                                 "11-01-refractive/scene8.crtscene", "09-03-reflective/scene4.crtscene"])
+def test_flattened_scene_matches_live_reference_dump(crt, ot, rel):
+    if not ot.have_reference_build():
+        pytest.skip("oracle/_ref not built")
+    scene = crt.Scene.load_file(ot.scene_file(rel))
+    ref = ot.run_harness(ot.scene_file(rel), dump=True)
+    assert ref["loaded"]
+    assert ot.compare_flat_with_dump(scene.flatten(), ref["dump"]) == []
+
+
+@needs_scenes
+@pytest.mark.parametrize("rel", otools.UNLOADABLE_SCENES)
+def test_scenes_the_reference_rejects_are_rejected(crt, ot, rel):
+    # missing materials / lights / material_index
+    with pytest.raises(crt.CrtError):
+        crt.Scene.load_file(ot.scene_file(rel))
+
+
+MINIMAL = {
+    "settings": {"background_color": [0, 0.5, 0], "image_settings": {"width": 8, "height": 4}},
+    "camera": {"matrix": [1, 0, 0, 0, 1, 0, 0, 0, 1], "position": [0, 0, 0]},
+    "lights": [{"intensity": 10, "position": [0, 1, 0]}],
+    "materials": [{"type": "diffuse", "albedo": [1, 0, 0], "smooth_shading": False}],
+    "objects": [{"material_index": 0, "vertices": [-1, -1, -3, 1, -1, -3, 0, 1, -3], "triangles": [0, 1, 2]}],
+}
+
+
+def _load(crt, doc):
+    return crt.Scene.load_json(json.dumps(doc) if not isinstance(doc, str) else doc)
+
+
+def test_minimal_scene_and_defaults(crt):
+    flat_owner = _load(crt, MINIMAL)
+    flat = flat_owner.flatten()
+    assert (flat.n_triangles, flat.n_vertices, flat.n_nodes, flat.n_refs, flat.n_lights) == (1, 3, 1, 1, 1)
+    assert (flat.gi_on, flat.reflections_on, flat.refractions_on, flat.bucket_size) == (0, 1, 1, 24)  # crt_json.cpp:616, crt_scene.h:16
+    assert flat.camera.tan_half_fov == pytest.approx(1.0, rel=1e-6)  # fov default 90 degrees
+    arr = flat.arrays()
+    assert np.allclose(arr["tri_verts"][0, :, 3], [0, 0, 1])  # face normal of a CCW triangle facing +z
+    assert arr["materials"][0, 1] == 0 and flat.n_textures == 1  # inline colour -> implicit albedo texture (crt_json.cpp:507-515)
+
+
+@pytest.mark.parametrize("mutate", [
+    lambda d: d.pop("materials"), lambda d: d.pop("lights"), lambda d: d.pop("objects"), lambda d: d.pop("camera"),
+    lambda d: d.pop("settings"), lambda d: d["settings"].pop("image_settings"), lambda d: d["settings"].pop("background_color"),
+    lambda d: d.update(materials=[]), lambda d: d["objects"][0].pop("material_index"),
+    lambda d: d["objects"][0].update(material_index=5), lambda d: d["objects"][0].update(triangles=[0, 1]),
+    lambda d: d["objects"][0].update(triangles=[0, 1, 2.5]), lambda d: d["objects"][0].update(triangles=[0, 1, 7]),
+    lambda d: d["objects"][0].update(vertices=[0, 1]), lambda d: d["objects"][0].update(uvs=[0, 0, 0]),
+    lambda d: d["materials"][0].pop("smooth_shading"), lambda d: d["materials"][0].update(type="glossy"),
+    lambda d: d["materials"][0].update(albedo="no such texture"), lambda d: d["camera"].update(matrix=[1, 0, 0]),
+    lambda d: d["settings"]["image_settings"].update(width=8.5), lambda d: d["settings"].update(gi_on=1),
+    lambda d: d["camera"].update(fov_degrees="wide"), lambda d: d["lights"][0].pop("intensity"),
+])
+def test_validation_failures_are_parse_errors(crt, mutate):
+    doc = json.loads(json.dumps(MINIMAL))
+    mutate(doc)
+    with pytest.raises(crt.CrtError, match="-4"):
+        _load(crt, doc)
+
+
+@pytest.mark.parametrize("text", ["", "   ", "{", "[1,2", '{"a":1,}', '{"a":1} x', "{'a':1}", '{"a":01}', '{"a":1.}', '{"a":.5}', '{"a":1e}',
+                                  '{"a":NaN}', '{"a":1e999}', '{"a":"\\x"}', '{"a":"\\ud800"}', "[1 2]", "nul"])
+def test_malformed_json_is_rejected(crt, text):
+    with pytest.raises(crt.CrtError):
+        crt.Scene.load_json(text)
+
+
+def test_number_conversion_follows_rapidjson(crt):
+    # every number goes through double -> float exactly as rapidjson's GetFloat(); spot values incl. long mantissas, exponents, -0
+    values = ["0.1", "-0.30000001192092896", "1e-3", "2.5E+2", "123456789.123456789", "0.000001", "16777217", "-0", "-0.0",
+              "3.4028234663852886e38", "1.17549435e-38", "0.333333333333333314829616256247", "4294967296", "18446744073709551616"]
+    doc = json.loads(json.dumps(MINIMAL))
+    text = json.dumps(doc).replace('"position": [0, 0, 0]', '"position": [0, 0, 0], "fov_degrees": 60')
+    for v in values:
+        t = text.replace('"intensity": 10', f'"intensity": {v}')
+        flat_owner = crt.Scene.load_json(t)
+        got = flat_owner.flatten().arrays()["lights"][0, 3]
+        want = np.float32(float(v))
+        assert got.tobytes() == want.tobytes() or (v == "-0" and got == 0 and not np.signbit(got)), (v, got, want)
+
+
+def test_texture_list_failure_voids_all_textures(crt):
+    # crt_json.cpp:582-588: a malformed entry drops the WHOLE list; inline-colour materials still load
+    doc = json.loads(json.dumps(MINIMAL))
+    doc["textures"] = [{"name": "ok", "type": "albedo", "albedo": [1, 1, 1]}, {"name": "bad", "type": "edges"}]
+    flat_owner = _load(crt, doc)
+    assert flat_owner.flatten().n_textures == 1
+    doc["materials"][0]["albedo"] = "ok"
+    with pytest.raises(crt.CrtError):
+        _load(crt, doc)
+
+
+def test_vertex_normals_are_renormalised_after_every_object(crt):
+    # crt_mesh.cpp:27-29: unreferenced vertices become NaN
+    doc = json.loads(json.dumps(MINIMAL))
+    doc["objects"][0]["vertices"] += [5, 5, 5]
+    n = _load(crt, doc).flatten().arrays()["vert_normal"]
+    assert np.isnan(n[3, :3]).all() and np.allclose(n[:3, :3], [0, 0, 1])
+
+
+def test_tree_rules_on_a_synthetic_grid(crt):
+    # leaf rule (<= 16 triangles or depth > 39), straddlers duplicated, absent child = -1, DFS pre-order numbering
+    rng = np.random.default_rng(7)
+    pts = rng.uniform(-4, 4, size=(300, 3)).astype(np.float32)
+    verts, tris = [], []
+    for i, p in enumerate(pts):
+        verts += [*p, *(p + [0.3, 0, 0]), *(p + [0, 0.3, 0])]
+        tris += [3 * i, 3 * i + 1, 3 * i + 2]
+    doc = json.loads(json.dumps(MINIMAL))
+    doc["objects"][0].update(vertices=[float(v) for v in verts], triangles=tris)
+    flat = _load(crt, doc).flatten()
+    a = flat.arrays()
+    box = a["box_nodes"]
+    left, right = box[:, 3], box[:, 7]
+    leaf = left <= -2
+    assert leaf.any() and (~leaf).any()
+    assert (right[leaf] > 0).all()
+    assert flat.n_refs == int(right[leaf].sum()) and flat.n_refs >= flat.n_triangles
+    first = -left[leaf] - 2
+    assert (np.diff(first) > 0).all() and first[0] == 0  # leaves own consecutive slices in DFS order
+    for i in np.nonzero(~leaf)[0]:
+        kids = [k for k in (left[i], right[i]) if k != -1]
+        assert kids and all(k > i for k in kids)
+        if left[i] != -1:
+            assert left[i] == i + 1  # child0 directly follows its parent (pre-order)
+    # every triangle is referenced, and only triangles whose box overlaps the leaf box
+    refs = a["refs"] & 0x7FFFFFFF
+    assert set(refs.tolist()) == set(range(flat.n_triangles))
+    mins, maxs = box[:, 0:3].view(np.float32), box[:, 4:7].view(np.float32)
+    tv = a["tri_verts"][:, :, :3]
+    for i in np.nonzero(leaf)[0][:50]:
+        for t in refs[-left[i] - 2: -left[i] - 2 + right[i]]:
+            assert (tv[t].min(0) <= maxs[i]).all() and (tv[t].max(0) >= mins[i]).all()

@@ -1,0 +1,176 @@
+"""Parity tests proper (-m gpu): the CUDA path, called through the C ABI, against the oracle on the same inputs.
+Bars (BASELINE.json): same primary hit triangle on >= 99.99 % of rays; PPM channel difference <= 1/255 on >= 99.9 %
+of pixels.  Where no libm function is involved we additionally demand BIT-IDENTICAL float framebuffers."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_tools as otools
+
+pytestmark = pytest.mark.gpu
+
+SIZES = {"15-01-conclusion/scene2.crtscene": (128, 128)}
+DEFAULT_SIZE = (480, 270)
+USES_LIBM = {"15-01-conclusion/scene2.crtscene"} | {f"11-01-refractive/scene{i}.crtscene" for i in range(9)}  # sinf/cosf (GI), powf (Fresnel)
+
+
+def same_bits(a, b):
+    return np.array_equal(otools.bits(a), otools.bits(b))
+
+
+def load(crt, ot, rel, size=None):
+    w, h = size or SIZES.get(rel, DEFAULT_SIZE)
+    scene = crt.Scene.load_json(ot.scene_variant(rel, w, h), os.path.dirname(ot.scene_file(rel)))
+    return scene, scene.flatten()
+
+
+def ppm_ok_fraction(a8, b8):
+    return float((np.abs(a8.astype(np.int32) - b8.astype(np.int32)).max(axis=2) <= 1).mean())
+
+
+@pytest.mark.parametrize("rel", otools.LOADABLE_SCENES)
+def test_scene_parity_all_modes(crt, ot, renderer, rel):
+    scene, flat = load(crt, ot, rel)
+    renderer.upload(flat)
+    want = ot.port_render(flat, crt.default_params())
+
+    # a1: ray generation is bit-identical
+    assert same_bits(renderer.primary_rays(), ot.port_primary_rays(flat))
+
+    # a2-a4, reference-order traversal: winners, distances AND the per-ray box / triangle test counts are identical
+    tri, t, nn, nt, _ = renderer.primary_hits(crt.TRAVERSAL_LITERAL)
+    assert np.array_equal(tri, want["tri"]) and same_bits(t, want["t"])
+    assert np.array_equal(nn, want["n_node"]) and np.array_equal(nt, want["n_tri"])
+
+    # fast k-d traversal: same winners (bar 99.99 %), same distances where the winner is the same
+    tri_kd, t_kd, nn_kd, nt_kd, _ = renderer.primary_hits(crt.TRAVERSAL_KD)
+    agree = tri_kd == want["tri"]
+    assert agree.mean() >= 0.9999, f"k-d traversal agrees on {agree.mean():.6f} of primary rays"
+    assert same_bits(t_kd[agree], want["t"][agree])
+    assert nt_kd.sum() <= nt.sum()  # never more triangle tests than the unpruned walk
+
+    # a17: brute force equals the tree (config 2) -- bit-exact winner and distance vs the oracle's brute force
+    brute = ot.port_primary_hits(flat, brute=True)
+    tri_b, t_b, _, _, _ = renderer.primary_hits(crt.TRAVERSAL_BRUTE)
+    assert np.array_equal(tri_b, brute["tri"]) and same_bits(t_b, brute["t"])
+
+    # full shading, both traversals and every pipeline that accepts the scene
+    for traversal in (crt.TRAVERSAL_LITERAL, crt.TRAVERSAL_KD):
+        for pipeline in (crt.PIPELINE_MEGAKERNEL, crt.PIPELINE_WAVEFRONT):
+            if pipeline == crt.PIPELINE_WAVEFRONT and (flat.gi_on or os.environ.get("CRT_TEST_SKIP_WAVEFRONT")):
+                continue
+            rgb, rgb8, stats = renderer.render(crt.default_params(traversal=traversal, pipeline=pipeline, collect_stats=1))
+            frac = ppm_ok_fraction(rgb8, want["rgb8"])
+            assert frac >= 0.999, f"{rel} traversal={traversal} pipeline={pipeline}: {frac:.6f} of pixels within 1/255"
+            identical = (otools.bits(rgb) == otools.bits(want["rgb"])).all(axis=2).mean()
+            if traversal == crt.TRAVERSAL_LITERAL:
+                assert stats["rays"] == want["stats"]["rays"], (stats["rays"], want["stats"]["rays"])
+                assert stats["rays_by_depth"] == want["stats"]["rays_by_depth"]
+                if rel not in USES_LIBM:
+                    assert identical == 1.0, f"{rel} pipeline={pipeline}: {identical:.6f} of float pixels bit-identical"
+                    assert stats["node_tests"] == want["stats"]["node_tests"] and stats["tri_tests"] == want["stats"]["tri_tests"]
+                else:
+                    assert identical >= 0.999, f"{rel} pipeline={pipeline}: only {identical:.6f} bit-identical (libm scenes)"
+            else:
+                assert identical >= 0.999
+            # the u8 output is the float output through write_ppm's rule
+            q = np.clip(np.trunc(np.nan_to_num(rgb.astype(np.float32) * np.float32(255), nan=-1.0)), 0, 255).astype(np.uint8)
+            assert np.array_equal(q, rgb8)
+
+
+@pytest.mark.parametrize("rel,kw", [
+    ("11-01-refractive/scene8.crtscene", dict(max_ray_depth=8)),
+    ("11-01-refractive/scene3.crtscene", dict(max_ray_depth=0)),
+    ("15-01-conclusion/scene1.crtscene", dict(max_ray_depth=1, reflection_bias=0.05)),
+    ("15-01-conclusion/scene2.crtscene", dict(diffuse_reflection_ray_count=2, max_ray_depth=2)),
+    ("15-01-conclusion/scene2.crtscene", dict(diffuse_reflection_ray_count=0)),
+    ("14-01-acceleration-tree/scene1.crtscene", dict(shadows=1)),
+    ("11-01-refractive/scene8.crtscene", dict(shadows=1)),
+])
+def test_non_default_settings(crt, ot, renderer, rel, kw):
+    scene, flat = load(crt, ot, rel, (320, 180) if "scene2" not in rel else (96, 96))
+    renderer.upload(flat)
+    params = crt.default_params(traversal=crt.TRAVERSAL_LITERAL, collect_stats=1, **kw)
+    want = ot.port_render(flat, params, primary=False)
+    rgb, rgb8, stats = renderer.render(params)
+    assert stats["rays"] == want["stats"]["rays"] and stats["shadow_rays"] == want["stats"]["shadow_rays"]
+    assert ppm_ok_fraction(rgb8, want["rgb8"]) >= 0.999
+    rgb_kd, rgb8_kd, _ = renderer.render(crt.default_params(traversal=crt.TRAVERSAL_KD, **kw))
+    assert ppm_ok_fraction(rgb8_kd, want["rgb8"]) >= 0.999
+
+
+def test_scene_flags_off(crt, ot, renderer):
+    # reflections_on / refractions_on = false (crt_renderer.cpp:106, :110-111)
+    for rel, flag in (("15-01-conclusion/scene1.crtscene", "reflections_on"), ("11-01-refractive/scene8.crtscene", "refractions_on")):
+        scene = crt.Scene.load_json(ot.scene_variant(rel, 320, 180, **{flag: False}))
+        flat = scene.flatten()
+        renderer.upload(flat)
+        want = ot.port_render(flat, crt.default_params(), primary=False)
+        rgb, _, _ = renderer.render(crt.default_params(traversal=crt.TRAVERSAL_LITERAL))
+        assert same_bits(rgb, want["rgb"])
+
+
+def test_full_size_c1_against_the_reference_itself(crt, ot, renderer):
+    """Config 1/2 at native 1920x1080 against the unmodified reference (oracle/_ref) -- not just the port."""
+    rel = "14-01-acceleration-tree/scene1.crtscene"
+    scene = crt.Scene.load_file(ot.scene_file(rel))
+    flat = scene.flatten()
+    renderer.upload(flat)
+    if ot.have_reference_build():
+        ref = ot.run_harness(ot.scene_file(rel), render=True, hits=True)
+        want_rgb, want_tri = ref["rgb"], ref["tri"]
+    else:
+        out = ot.port_render(flat, crt.default_params())
+        want_rgb, want_tri = out["rgb"], out["tri"]
+    for traversal in (crt.TRAVERSAL_LITERAL, crt.TRAVERSAL_KD):
+        rgb, _, _ = renderer.render(crt.default_params(traversal=traversal))
+        tri, _, _, _, _ = renderer.primary_hits(traversal, counters=False)
+        assert (tri == want_tri).mean() >= 0.9999
+        if traversal == crt.TRAVERSAL_LITERAL:
+            assert np.array_equal(tri, want_tri) and same_bits(rgb, want_rgb)
+        else:
+            assert (otools.bits(rgb) == otools.bits(want_rgb)).all(axis=2).mean() >= 0.9999
+
+
+def test_edge_cases(crt, ot, renderer):
+    import json
+    base = json.loads(ot.scene_variant("14-01-acceleration-tree/scene0.crtscene", 37, 19))  # ragged: not a multiple of the 16x8 tile
+    scene = crt.Scene.load_json(json.dumps(base))
+    flat = scene.flatten()
+    renderer.upload(flat)
+    want = ot.port_render(flat, crt.default_params(), primary=False)
+    rgb, _, _ = renderer.render(crt.default_params())
+    assert rgb.shape == (19, 37, 3) and same_bits(rgb, want["rgb"])
+    # no geometry at all: every pixel is the background
+    base["objects"] = []
+    scene = crt.Scene.load_json(json.dumps(base))
+    flat = scene.flatten()
+    renderer.upload(flat)
+    for traversal in (crt.TRAVERSAL_LITERAL, crt.TRAVERSAL_KD):
+        rgb, _, stats = renderer.render(crt.default_params(traversal=traversal, collect_stats=1))
+        assert (rgb == np.array(list(flat.background), np.float32)).all() and stats["rays"] == 37 * 19
+    # 1x1 and empty images
+    for w, h in ((1, 1), (0, 0)):
+        base["settings"]["image_settings"].update(width=w, height=h)
+        scene = crt.Scene.load_json(json.dumps(base))
+        renderer.upload(scene.flatten())
+        rgb, _, _ = renderer.render(crt.default_params())
+        assert rgb.shape == (h, w, 3)
+
+
+def test_band_ownership_reassembles_the_frame(crt, ot, renderer):
+    """multi-GPU stills: each rank renders its row bands into a compact buffer; the union is the full frame"""
+    scene, flat = load(crt, ot, "15-01-conclusion/scene1.crtscene", (322, 181))
+    renderer.upload(flat)
+    full, full8, _ = renderer.render(crt.default_params())
+    for world, band in ((2, 8), (3, 5), (8, 8)):
+        out = np.zeros_like(full)
+        seen = np.zeros(full.shape[0], np.int32)
+        for rank in range(world):
+            part, _, stats = renderer.render(crt.default_params(rank=rank, world=world, band_rows=band))
+            rows = crt.Renderer.owned_rows(full.shape[0], rank, world, band)
+            assert stats["rows_rendered"] == len(rows) == part.shape[0]
+            out[rows] = part
+            seen[rows] += 1
+        assert (seen == 1).all() and same_bits(out, full)
