@@ -219,7 +219,12 @@ class Renderer:
             raise CrtError(f"{what} -> {rc}: {lib.crt_cuda_last_error(self._ctx).decode()}")
 
     def set_stream(self, stream_ptr: int | None):
-        self._check(lib.crt_cuda_set_stream(self._ctx, C.c_void_p(stream_ptr or 0)), "crt_cuda_set_stream")
+        """None = the context's own stream; 0 (torch's default stream) is passed as cudaStreamLegacy (handle 1)."""
+        if stream_ptr is None:
+            handle = 0
+        else:
+            handle = stream_ptr if stream_ptr != 0 else 1
+        self._check(lib.crt_cuda_set_stream(self._ctx, C.c_void_p(handle)), "crt_cuda_set_stream")
 
     def upload(self, scene: Scene | FlatScene):
         flat = scene.flatten() if isinstance(scene, Scene) else scene

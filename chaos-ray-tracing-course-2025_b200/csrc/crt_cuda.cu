@@ -22,6 +22,9 @@ struct crt_cuda_ctx {
     size_t h_arena_cap = 0;
     DScene scene{};
     bool have_scene = false;
+    bool has_secondary = false; // some material can spawn reflection / refraction rays
+    crt_render_params last_params{};
+    bool last_wavefront = false;
 
     float *d_rgb = nullptr;
     uint8_t *d_rgb8 = nullptr;
@@ -147,6 +150,8 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     ctx->last_width = W;
     ctx->last_rows = dp.rows;
     ctx->last_launches = 0;
+    ctx->last_wavefront = false;
+    ctx->last_params = *params;
     if (stats)
         CRT_CK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), ctx->stream));
     CRT_CK(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
@@ -159,8 +164,9 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
             return fail(ctx, CRT_ERR_INVALID, "the wavefront pipeline does not handle GI or shadow rays; use CRT_PIPELINE_MEGAKERNEL");
         if (pipeline == CRT_PIPELINE_WAVEFRONT) {
             int launches = 0;
-            cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, ctx->stream,
-                                             &launches);
+            cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
+                                             ctx->d_counters, ctx->stream, &launches);
+            ctx->last_wavefront = true;
             if (e != cudaSuccess)
                 return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
             ctx->last_launches = launches;
@@ -343,6 +349,10 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     d.materials = reinterpret_cast<const int4 *>(ctx->d_arena + parts[8].offset);
     d.textures = reinterpret_cast<const float4 *>(ctx->d_arena + parts[9].offset);
     d.texels = reinterpret_cast<const float4 *>(ctx->d_arena + parts[10].offset);
+    ctx->has_secondary = false;
+    for (int i = 0; i < s->n_materials; ++i)
+        if ((s->materials[i].type == 1 && s->reflections_on) || (s->materials[i].type == 2 && s->refractions_on))
+            ctx->has_secondary = true;
     ctx->have_scene = true;
     return CRT_OK;
 }
@@ -375,6 +385,15 @@ int crt_cuda_synchronize(crt_cuda_ctx *ctx, crt_render_stats *stats) {
         return CRT_ERR_INVALID;
     CRT_CK(ctx, cudaSetDevice(ctx->device));
     CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    // a bounce level outgrew the ray pool: grow it and render the frame again (rare; the pool then stays large)
+    for (int attempt = 0; ctx->last_wavefront && ctx->wf.h_flags && *ctx->wf.h_flags && attempt < 6; ++attempt) {
+        *ctx->wf.h_flags = 0;
+        ctx->wf.grow *= 2.0;
+        const crt_render_params again = ctx->last_params;
+        if (int rc = enqueue_frame(ctx, &again))
+            return rc;
+        CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     float ms = 0.0f;
     if (stats && ctx->last_width)
         cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end);

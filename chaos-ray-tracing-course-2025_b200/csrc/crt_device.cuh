@@ -192,63 +192,94 @@ __device__ __forceinline__ Hit trace_literal(const DScene &S, const Ray &r, Coun
 // parse-order index (always the lowest index in practice).  Decisions carry a small
 // slack so that grazing cases visit a SUPERSET of the reference's leaves (extra leaves cannot change the winner:
 // any triangle hit found there is also referenced by the leaf that contains the hit point).
-template <bool STATS>
-__device__ __forceinline__ Hit trace_kd(const DScene &S, const Ray &r, Counters *cn) {
-    Hit best{ kInf, -1 };
-    const V3 o = r.o, d = r.d;
-    if (!(d.x == d.x && d.y == d.y && d.z == d.z))
-        return best; // NaN direction (refraction at normal incidence, crt_vector.cpp:11-27): every compare is false
-    const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    float tmin = 0.0f, tmax = kInf;
-    {
+//
+// The walk is a resumable state machine (KdWalker) so that the wavefront trace kernel can interleave "replace a
+// finished ray" with "advance to the next leaf"; trace_kd() simply runs it to completion.
+//
+// Mailbox: the reference's builder references a straddling triangle from every leaf it overlaps (38 references
+// per triangle in the 1 M-triangle scene), so consecutive leaves along a ray hold mostly the same triangles.
+// A small direct-mapped per-ray table of already-tested triangle ids (shared memory, [slot][thread] layout =
+// conflict-free) skips the repeats; a repeat test would return the same t, so results are unchanged.
+constexpr int kMailboxSlots = 16;
+
+struct KdWalker {
+    V3 o, d, inv;
+    float tmin, tmax;
+    int node; // node to visit next, or -1 when the walk is finished
+    int sp;
+    Hit best;
+    int snode[kStack];
+    float smin[kStack], smax[kStack];
+
+    // false: the ray misses the root box (or has a NaN direction) and the walk is already finished
+    template <bool STATS>
+    __device__ __forceinline__ bool init(const DScene &S, const Ray &r, Counters *cn) {
+        best = Hit{ kInf, -1 };
+        node = -1;
+        sp = 0;
+        o = r.o, d = r.d;
+        if (!(d.x == d.x && d.y == d.y && d.z == d.z))
+            return false; // NaN direction (refraction at normal incidence, crt_vector.cpp:11-27): every compare is false
+        inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+        tmin = 0.0f, tmax = kInf;
         const float lx = S.root_min[0], ly = S.root_min[1], lz = S.root_min[2], hx = S.root_max[0], hy = S.root_max[1], hz = S.root_max[2];
         if (d.x != 0.0f) {
             const float a = (lx - o.x) * inv.x, b = (hx - o.x) * inv.x;
             tmin = fmaxf(tmin, fminf(a, b));
             tmax = fminf(tmax, fmaxf(a, b));
         } else if (o.x < lx || o.x > hx)
-            return best;
+            return false;
         if (d.y != 0.0f) {
             const float a = (ly - o.y) * inv.y, b = (hy - o.y) * inv.y;
             tmin = fmaxf(tmin, fminf(a, b));
             tmax = fminf(tmax, fmaxf(a, b));
         } else if (o.y < ly || o.y > hy)
-            return best;
+            return false;
         if (d.z != 0.0f) {
             const float a = (lz - o.z) * inv.z, b = (hz - o.z) * inv.z;
             tmin = fmaxf(tmin, fminf(a, b));
             tmax = fminf(tmax, fmaxf(a, b));
         } else if (o.z < lz || o.z > hz)
-            return best;
+            return false;
+        if (STATS)
+            ++cn->node_tests;
+        tmax = tmax + (fabsf(tmax) * 1e-5f + 1e-6f);
+        if (tmin > tmax)
+            return false;
+        node = 0;
+        return true;
     }
-    if (STATS)
-        ++cn->node_tests;
-    tmax = tmax + (fabsf(tmax) * 1e-5f + 1e-6f);
-    if (tmin > tmax)
-        return best;
 
-    int snode[kStack];
-    float smin[kStack], smax[kStack];
-    int sp = 0;
-    int node = 0;
-    for (;;) {
-        bool pop = false;
-        const int4 n = __ldg(&S.kd_nodes[node]);
-        if (n.w == 3) {
-            for (int i = 0; i < n.z; ++i) {
-                const uint32_t ref = __ldg(&S.refs[n.y + i]);
-                const int tri = int(ref & 0x7FFFFFFFu);
-                const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
-                if (STATS)
-                    ++cn->tri_tests;
-                float t;
-                if (triangle_test(A, B, C, (ref >> 31) != 0, r, t) && (t < best.t || (t == best.t && tri < best.tri))) {
-                    best.t = t;
-                    best.tri = tri;
-                }
+    __device__ __forceinline__ bool done() const { return node < 0; }
+
+    // pop the next pending subtree that can still hold a closer (or equal) hit; node = -1 when none is left
+    template <bool STATS>
+    __device__ __forceinline__ void pop(Counters *cn) {
+        for (;;) {
+            if (sp == 0) {
+                node = -1;
+                return;
             }
-            pop = true;
-        } else {
+            --sp;
+            node = snode[sp];
+            tmin = smin[sp];
+            tmax = smax[sp];
+            // strict pruning with slack: entries that start clearly beyond the best hit cannot beat or tie it
+            if (!(tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best.t))
+                break;
+        }
+        if (STATS)
+            ++cn->node_tests;
+    }
+
+    // descend from `node` to the next leaf (pushing far children); returns the leaf's kd node, or w = -1 if the
+    // walk ran out of nodes on the way
+    template <bool STATS>
+    __device__ __forceinline__ int4 descend(const DScene &S, Counters *cn) {
+        for (;;) {
+            const int4 n = __ldg(&S.kd_nodes[node]);
+            if (n.w == 3)
+                return n;
             const int axis = n.w;
             const float split = __int_as_float(n.x);
             const float oa = pick(o, axis), da = pick(d, axis), ia = pick(inv, axis);
@@ -284,25 +315,61 @@ __device__ __forceinline__ Hit trace_kd(const DScene &S, const Ray &r, Counters 
                 node = next;
                 if (STATS)
                     ++cn->node_tests;
-            } else
-                pop = true;
-        }
-        if (pop) {
-            for (;;) {
-                if (sp == 0)
-                    return best;
-                --sp;
-                node = snode[sp];
-                tmin = smin[sp];
-                tmax = smax[sp];
-                // strict pruning with slack: entries that start clearly beyond the best hit cannot beat or tie it
-                if (!(tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best.t))
-                    break;
+            } else {
+                pop<STATS>(cn);
+                if (node < 0)
+                    return make_int4(0, 0, 0, -1);
             }
-            if (STATS)
-                ++cn->node_tests;
         }
     }
+
+    // test one leaf reference against the ray (mailbox = this thread's column of the shared table, or nullptr)
+    template <bool STATS>
+    __device__ __forceinline__ void test_ref(const DScene &S, uint32_t ref, Counters *cn, int *mailbox, int mailbox_stride) {
+        const int tri = int(ref & 0x7FFFFFFFu);
+        if (mailbox) {
+            int *slot = mailbox + ((uint32_t(tri) * 0x9E3779B1u) >> 28) * mailbox_stride;
+            if (*slot == tri)
+                return;
+            *slot = tri;
+        }
+        const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
+        if (STATS)
+            ++cn->tri_tests;
+        float t;
+        if (triangle_test(A, B, C, (ref >> 31) != 0, Ray{ o, d }, t) && (t < best.t || (t == best.t && tri < best.tri))) {
+            best.t = t;
+            best.tri = tri;
+        }
+    }
+
+    // one unit of work: descend to the next leaf, test its triangles, pop.  Call while !done().
+    template <bool STATS>
+    __device__ __forceinline__ void advance(const DScene &S, Counters *cn, int *mailbox, int mailbox_stride) {
+        const int4 leaf = descend<STATS>(S, cn);
+        if (leaf.w < 0)
+            return;
+        for (int i = 0; i < leaf.z; ++i)
+            test_ref<STATS>(S, __ldg(&S.refs[leaf.y + i]), cn, mailbox, mailbox_stride);
+        pop<STATS>(cn);
+    }
+};
+
+__device__ __forceinline__ void mailbox_clear(int *mailbox, int mailbox_stride) {
+    if (mailbox)
+        for (int k = 0; k < kMailboxSlots; ++k)
+            mailbox[k * mailbox_stride] = -1;
+}
+
+template <bool STATS>
+__device__ __forceinline__ Hit trace_kd(const DScene &S, const Ray &r, Counters *cn, int *mailbox = nullptr, int mailbox_stride = 0) {
+    KdWalker w;
+    if (w.init<STATS>(S, r, cn)) {
+        mailbox_clear(mailbox, mailbox_stride);
+        while (!w.done())
+            w.advance<STATS>(S, cn, mailbox, mailbox_stride);
+    }
+    return w.best;
 }
 
 // Brute force over every triangle in parse order with strict '<' (ray_intersect_triangle_span over the whole

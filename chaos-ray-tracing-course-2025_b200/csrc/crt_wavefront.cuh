@@ -1,17 +1,419 @@
-// Wavefront pipeline (ray queues + compaction between bounce stages).  Placeholder interface: filled in next.
+// Wavefront pipeline: per bounce level one TRACE kernel (persistent warps, finished rays are replaced lane by lane
+// from the level's queue) and one SHADE kernel (one thread per ray, emits the next level's rays with warp-aggregated
+// ballot/shfl compaction), then a bottom-up RESOLVE that combines child colours in exactly the nesting of the
+// reference's recursion (src/core/crt_renderer.cpp:103-135), so float results stay bit-identical to the depth-first
+// evaluation.  Handles every material except GI (one PCG stream per pixel consumed depth-first -> megakernel) and the
+// flagged shadow mode.
+//
+// Node ids: level-0 nodes are pixel SLOTS s in [0, P) (P = padded pixel count, 8x4-patch-major order so consecutive
+// slots are image neighbours); level >= 1 nodes are P + q, q in [0, cap), allocated level by level, so a level's
+// nodes are contiguous: [P + start(L), P + start(L) + count[L]).
 #pragma once
+
 #include "crt_kernels.cuh"
 
 namespace crtdev {
 
-constexpr bool kWavefrontReady = false;
+constexpr bool kWavefrontReady = true;
+constexpr int kMaxLevels = kMaxDepthCap + 2;
 
-struct WavefrontState {};
+struct WfCtl {                 // zeroed at the start of every frame
+    int count[kMaxLevels];     // rays per level (level 0 is implicit = P)
+    int fetch[kMaxLevels];     // trace kernels' queue cursors
+    int pending0;              // non-terminal pixels (entries of `pend`)
+    int overflow;              // a level outgrew the pool: the host retries with a larger one
+};
 
-inline void wavefront_free(WavefrontState &) {}
+struct WfBuffers {
+    float4 *ray_o, *ray_d; // [cap]      rays of levels >= 1 (w of ray_o: unused)
+    float2 *hit;           // [P + cap]  {t, tri as int bits}
+    int4 *rec;             // [P + cap]  {kind, first child node id, fresnel bits, 0}
+    float4 *alb;           // [P + cap]  reflective albedo
+    float4 *col;           // [P + cap]  resolved colour of a node
+    int *pend;             // [P]        slots of non-terminal pixels
+    WfCtl *ctl;
+    int P, cap, patches_x;
+};
 
-inline cudaError_t wavefront_render(WavefrontState &, const DScene &, const DParams &, int, bool, float *, uint8_t *, Counters *, cudaStream_t, int *) {
-    return cudaErrorNotSupported;
+struct WavefrontState {
+    WfBuffers b{};
+    size_t node_capacity = 0; // allocated entries of hit/rec/alb/col
+    size_t ray_capacity = 0;  // allocated entries of ray_o/ray_d
+    size_t pend_capacity = 0;
+    int sm_count = 0;
+    int *h_flags = nullptr;   // pinned: {overflow}
+    double grow = 1.0;        // pool = grow * pixels
+};
+
+enum NodeKind : int { kTerminal = 0, kNodeReflect = 1, kNodeRefract = 2, kNodeTir = 3 };
+
+__device__ __forceinline__ int level_start(const WfCtl *ctl, int level) { // q-offset of a level (level >= 1)
+    int s = 0;
+    for (int l = 1; l < level; ++l)
+        s += ctl->count[l];
+    return s;
+}
+
+// slot -> pixel.  Slots run patch by patch (8 wide, 4 tall), patches row-major.
+__device__ __forceinline__ bool slot_pixel(const WfBuffers &b, const DScene &S, const DParams &P, int slot, int &x, int &ly) {
+    const int patch = slot >> 5, lane = slot & 31;
+    x = (patch % b.patches_x) * 8 + (lane & 7);
+    ly = (patch / b.patches_x) * 4 + (lane >> 3);
+    return x < S.cam.width && ly < P.rows;
+}
+
+// ------------------------------------------------------------------------------------------------ TRACE
+// Persistent warps.  Each lane owns one ray at a time; when fewer than kRefillBelow lanes still have work the
+// idle lanes take the next rays of the queue (one atomicAdd per warp, ballot + popc for the lane offsets).
+constexpr int kTraceBlock = 128;
+constexpr int kRefillBelow = 25;
+
+template <int TRAV, bool STATS>
+__global__ void __launch_bounds__(kTraceBlock) k_wf_trace(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
+                                                          const __grid_constant__ WfBuffers b, int level, Counters *__restrict__ counters) {
+    __shared__ int mailbox_mem[kMailboxSlots * kTraceBlock];
+    int *mailbox = mailbox_mem + threadIdx.x;
+    WfCtl *ctl = b.ctl;
+    const int total = level == 0 ? b.P : ctl->count[level];
+    const int start = level == 0 ? 0 : level_start(ctl, level);
+    const unsigned lane = threadIdx.x & 31u;
+    Counters cn{};
+    KdWalker w;
+    w.node = -1;
+    int my = -1; // index of my ray within the level, -1 = idle
+    bool exhausted = false;
+    for (;;) {
+        const unsigned busy = __ballot_sync(0xffffffffu, my >= 0);
+        if (!exhausted && __popc(busy) < kRefillBelow) {
+            const unsigned idle = ~busy;
+            int base = 0;
+            if (lane == 0)
+                base = atomicAdd(&ctl->fetch[level], __popc(idle));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + __popc(idle) >= total)
+                exhausted = true;
+            if (my < 0) {
+                const int i = base + __popc(idle & ((1u << lane) - 1u));
+                if (i < total) {
+                    Ray r;
+                    bool have = true;
+                    if (level == 0) {
+                        int x, ly;
+                        have = slot_pixel(b, S, P, i, x, ly);
+                        if (have)
+                            r = generate_ray(S.cam, x, global_row(P, ly));
+                    } else {
+                        r = Ray{ xyz(b.ray_o[start + i]), xyz(b.ray_d[start + i]) };
+                    }
+                    if (have) {
+                        if (STATS) {
+                            ++cn.rays;
+                            ++cn.rays_by_depth[level];
+                        }
+                        my = i;
+                        if (TRAV == CRT_TRAVERSAL_KD) {
+                            if (w.init<STATS>(S, r, &cn))
+                                mailbox_clear(mailbox, kTraceBlock);
+                        } else {
+                            // verification traversal: run the reference-order walk to completion right here
+                            w.best = trace_literal<STATS>(S, r, &cn);
+                            w.node = -1;
+                        }
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, my >= 0) == 0u) {
+            if (exhausted)
+                break;
+            continue;
+        }
+        if (my >= 0) {
+            if (TRAV == CRT_TRAVERSAL_KD && !w.done())
+                w.advance<STATS>(S, &cn, mailbox, kTraceBlock);
+            if (w.done()) {
+                const int node_id = level == 0 ? my : b.P + start + my;
+                b.hit[node_id] = make_float2(w.best.t, __int_as_float(w.best.tri));
+                my = -1;
+            }
+        }
+    }
+    if (STATS)
+        flush_counters(cn, counters);
+}
+
+// ------------------------------------------------------------------------------------------------ SHADE
+__device__ __forceinline__ void write_pixel(const DScene &S, float *__restrict__ rgb, uint8_t *__restrict__ rgb8, int x, int ly, V3 c) {
+    const size_t i = (size_t(ly) * S.cam.width + x) * 3;
+    if (rgb)
+        rgb[i] = c.x, rgb[i + 1] = c.y, rgb[i + 2] = c.z;
+    if (rgb8)
+        rgb8[i] = quantize(c.x), rgb8[i + 1] = quantize(c.y), rgb8[i + 2] = quantize(c.z);
+}
+
+constexpr int kShadeBlock = 128;
+
+__global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
+                                                          const __grid_constant__ WfBuffers b, int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
+    WfCtl *ctl = b.ctl;
+    const int total = level == 0 ? b.P : ctl->count[level];
+    const int start = level == 0 ? 0 : level_start(ctl, level);
+    const int next_start = level == 0 ? 0 : start + total;
+    const unsigned lane = threadIdx.x & 31u;
+    const V3 zero = mk(0.0f, 0.0f, 0.0f);
+    // warp-uniform trip count: every lane of a warp runs the same iterations, so the collectives below are safe
+    for (int first = (blockIdx.x * kShadeBlock + (threadIdx.x & ~31)); first < total; first += gridDim.x * kShadeBlock) {
+        const int i = first + int(lane);
+        int x = 0, ly = 0;
+        bool have = i < total;
+        if (have && level == 0)
+            have = slot_pixel(b, S, P, i, x, ly);
+        const int node_id = level == 0 ? i : b.P + start + i;
+        int kind = kTerminal, children = 0;
+        V3 c = zero, albedo = zero, o0 = zero, d0 = zero, o1 = zero, d1 = zero;
+        float fres = 0.0f;
+        if (have) {
+            Ray ray;
+            if (level == 0)
+                ray = generate_ray(S.cam, x, global_row(P, ly));
+            else
+                ray = Ray{ xyz(b.ray_o[start + i]), xyz(b.ray_d[start + i]) };
+            const float2 hrec = b.hit[node_id];
+            const Hit h{ hrec.x, __float_as_int(hrec.y) };
+            const bool last = uint32_t(level) >= P.max_ray_depth; // children would be beyond max depth: black (crt_renderer.cpp:47-48)
+            if (h.tri < 0) {
+                c = mk(S.bg[0], S.bg[1], S.bg[2]);
+            } else {
+                const Surface s = make_surface(S, ray, h);
+                const int4 m = __ldg(&S.materials[s.material]);
+                if (m.x == 0) {
+                    c = add_direct_light(S, zero, s, sample_texture(S, m.y, s), [](V3, float) { return false; }) / float(P.gi_rays + 1u);
+                } else if (m.x == 1) {
+                    albedo = sample_texture(S, m.y, s);
+                    if (!S.reflections_on) {
+                        c = albedo;
+                    } else if (last) {
+                        c = tint(albedo, zero);
+                    } else {
+                        kind = kNodeReflect, children = 1;
+                        o0 = s.P + s.n * P.reflection_bias, d0 = reflect(ray.d, s.n);
+                    }
+                } else if (m.x == 2) {
+                    if (S.refractions_on) {
+                        V3 n = s.n;
+                        float outside = 1.0f, inside = __int_as_float(m.z);
+                        if (dot(ray.d, n) > 0.0f) {
+                            n = -n;
+                            const float tmp = outside;
+                            outside = inside, inside = tmp;
+                        }
+                        V3 rd = ray.d;
+                        const bool refracted = refract(rd, n, outside, inside);
+                        fres = fresnel_term(1.0f + dot(ray.d, n));
+                        if (last) {
+                            c = refracted ? zero * fres + zero * (1.0f - fres) : zero;
+                        } else {
+                            kind = refracted ? kNodeRefract : kNodeTir;
+                            children = refracted ? 2 : 1;
+                            o0 = s.P + n * P.reflection_bias, d0 = reflect(ray.d, n);
+                            o1 = s.P + (-n) * 1e-2f, d1 = rd; // refraction bias is always the default (crt_ray.h:33)
+                        }
+                    }
+                } else {
+                    c = sample_texture(S, m.y, s);
+                }
+            }
+        }
+        // ---- warp-aggregated allocation of the children in the next level's queue (ballot/shfl compaction)
+        int prefix = children;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, prefix, o);
+            if (int(lane) >= o)
+                prefix += v;
+        }
+        const int warp_total = __shfl_sync(0xffffffffu, prefix, 31);
+        int base = 0;
+        if (warp_total) {
+            if (lane == 0)
+                base = atomicAdd(&ctl->count[level + 1], warp_total);
+            base = __shfl_sync(0xffffffffu, base, 0);
+        }
+        const unsigned pend_mask = __ballot_sync(0xffffffffu, level == 0 && children > 0);
+        int pend_base = 0;
+        if (pend_mask) {
+            if (lane == 0)
+                pend_base = atomicAdd(&ctl->pending0, __popc(pend_mask));
+            pend_base = __shfl_sync(0xffffffffu, pend_base, 0);
+        }
+        if (!have)
+            continue;
+        if (children) {
+            const int q = next_start + base + (prefix - children);
+            if (q + children > b.cap) {
+                ctl->overflow = 1;
+                kind = kTerminal, children = 0, c = zero; // frame is discarded and re-rendered with a larger pool
+            } else {
+                b.ray_o[q] = make_float4(o0.x, o0.y, o0.z, 0.0f);
+                b.ray_d[q] = make_float4(d0.x, d0.y, d0.z, 0.0f);
+                if (children == 2) {
+                    b.ray_o[q + 1] = make_float4(o1.x, o1.y, o1.z, 0.0f);
+                    b.ray_d[q + 1] = make_float4(d1.x, d1.y, d1.z, 0.0f);
+                }
+                b.rec[node_id] = make_int4(kind, b.P + q, __float_as_int(fres), 0);
+                b.alb[node_id] = make_float4(albedo.x, albedo.y, albedo.z, 0.0f);
+                if (level == 0)
+                    b.pend[pend_base + __popc(pend_mask & ((1u << lane) - 1u))] = i;
+            }
+        }
+        if (!children) {
+            if (level == 0) {
+                write_pixel(S, rgb, rgb8, x, ly, c);
+            } else {
+                b.rec[node_id].x = kTerminal;
+                b.col[node_id] = make_float4(c.x, c.y, c.z, 0.0f);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ RESOLVE
+__device__ __forceinline__ V3 combine(const WfBuffers &b, const int4 rec, int node_id) {
+    const V3 c0 = xyz(b.col[rec.y]);
+    if (rec.x == kNodeReflect)
+        return tint(xyz(b.alb[node_id]), c0); // albedo * shade(reflection), crt_renderer.cpp:106
+    if (rec.x == kNodeTir)
+        return c0; // :133
+    const float f = __int_as_float(rec.z);
+    return c0 * f + xyz(b.col[rec.y + 1]) * (1.0f - f); // :131
+}
+
+__global__ void __launch_bounds__(256) k_wf_resolve(const __grid_constant__ DScene S, const __grid_constant__ DParams P, const __grid_constant__ WfBuffers b,
+                                                    int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
+    const WfCtl *ctl = b.ctl;
+    if (level == 0) {
+        const int total = ctl->pending0;
+        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x) {
+            const int slot = b.pend[k];
+            int x, ly;
+            slot_pixel(b, S, P, slot, x, ly);
+            write_pixel(S, rgb, rgb8, x, ly, combine(b, b.rec[slot], slot));
+        }
+        return;
+    }
+    const int total = ctl->count[level], start = level_start(ctl, level);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x) {
+        const int node_id = b.P + start + k;
+        const int4 rec = b.rec[node_id];
+        if (rec.x != kTerminal) {
+            const V3 c = combine(b, rec, node_id);
+            b.col[node_id] = make_float4(c.x, c.y, c.z, 0.0f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host driver
+inline void wavefront_free(WavefrontState &w) {
+    cudaFree(w.b.ray_o), cudaFree(w.b.ray_d), cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col), cudaFree(w.b.pend),
+        cudaFree(w.b.ctl);
+    cudaFreeHost(w.h_flags);
+    w = WavefrontState{};
+}
+
+inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
+    cudaError_t e = cudaSuccess;
+    if (!w.b.ctl) {
+        if ((e = cudaMalloc(&w.b.ctl, sizeof(WfCtl))) != cudaSuccess)
+            return e;
+        if ((e = cudaHostAlloc(&w.h_flags, sizeof(int), cudaHostAllocDefault)) != cudaSuccess)
+            return e;
+        *w.h_flags = 0;
+        cudaDeviceProp prop;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaGetDeviceProperties(&prop, dev);
+        w.sm_count = prop.multiProcessorCount;
+    }
+    const size_t cap = secondary ? size_t(double(P) * w.grow) + 1024 : 0;
+    const size_t nodes = size_t(P) + cap;
+    if (nodes > w.node_capacity) {
+        cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col);
+        w.b.hit = nullptr, w.b.rec = nullptr, w.b.alb = nullptr, w.b.col = nullptr, w.node_capacity = 0;
+        if ((e = cudaMalloc(&w.b.hit, nodes * sizeof(float2))) != cudaSuccess)
+            return e;
+        if (secondary) {
+            if ((e = cudaMalloc(&w.b.rec, nodes * sizeof(int4))) != cudaSuccess)
+                return e;
+            if ((e = cudaMalloc(&w.b.alb, nodes * sizeof(float4))) != cudaSuccess)
+                return e;
+            if ((e = cudaMalloc(&w.b.col, nodes * sizeof(float4))) != cudaSuccess)
+                return e;
+        }
+        w.node_capacity = nodes;
+    }
+    if (cap > w.ray_capacity) {
+        cudaFree(w.b.ray_o), cudaFree(w.b.ray_d);
+        w.b.ray_o = nullptr, w.b.ray_d = nullptr, w.ray_capacity = 0;
+        if ((e = cudaMalloc(&w.b.ray_o, cap * sizeof(float4))) != cudaSuccess)
+            return e;
+        if ((e = cudaMalloc(&w.b.ray_d, cap * sizeof(float4))) != cudaSuccess)
+            return e;
+        w.ray_capacity = cap;
+    }
+    if (secondary && size_t(P) > w.pend_capacity) {
+        cudaFree(w.b.pend);
+        w.b.pend = nullptr, w.pend_capacity = 0;
+        if ((e = cudaMalloc(&w.b.pend, size_t(P) * sizeof(int))) != cudaSuccess)
+            return e;
+        w.pend_capacity = size_t(P);
+    }
+    w.b.P = P;
+    w.b.cap = int(cap);
+    return cudaSuccess;
+}
+
+template <int TRAV>
+inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, const DParams &dp, bool stats, int level, int blocks, Counters *counters,
+                                   cudaStream_t stream) {
+    if (stats)
+        k_wf_trace<TRAV, true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+    else
+        k_wf_trace<TRAV, false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+}
+
+// `secondary` = the scene can spawn reflection / refraction rays at all (known from its materials on the host)
+inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
+                                    uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches) {
+    const int patches_x = (S.cam.width + 7) / 8, patches_y = (dp.rows + 3) / 4;
+    const int P = patches_x * patches_y * 32;
+    secondary = secondary && dp.max_ray_depth > 0;
+    cudaError_t e = wavefront_reserve(w, P, secondary);
+    if (e != cudaSuccess)
+        return e;
+    w.b.patches_x = patches_x;
+    if ((e = cudaMemsetAsync(w.b.ctl, 0, sizeof(WfCtl), stream)) != cudaSuccess)
+        return e;
+    const int levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
+    const int trace_blocks = w.sm_count * 8;
+    int n = 0;
+    for (int level = 0; level < levels; ++level) {
+        const int tb = level == 0 ? min(trace_blocks, (P + kTraceBlock - 1) / kTraceBlock) : trace_blocks;
+        if (traversal == CRT_TRAVERSAL_LITERAL)
+            wavefront_launch_trace<CRT_TRAVERSAL_LITERAL>(w, S, dp, stats, level, tb, counters, stream);
+        else
+            wavefront_launch_trace<CRT_TRAVERSAL_KD>(w, S, dp, stats, level, tb, counters, stream);
+        const int sb = level == 0 ? min(w.sm_count * 32, (P + kShadeBlock - 1) / kShadeBlock) : w.sm_count * 8;
+        k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
+        n += 2;
+    }
+    for (int level = levels - 2; level >= 0; --level) {
+        k_wf_resolve<<<w.sm_count * 4, 256, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
+        ++n;
+    }
+    if (secondary)
+        e = cudaMemcpyAsync(w.h_flags, &w.b.ctl->overflow, sizeof(int), cudaMemcpyDeviceToHost, stream);
+    if (launches)
+        *launches = n;
+    return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 } // namespace crtdev

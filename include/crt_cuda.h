@@ -178,7 +178,8 @@ int crt_cuda_device_count(void);
 int crt_cuda_create(int device, crt_cuda_ctx **out);
 void crt_cuda_destroy(crt_cuda_ctx *ctx);
 const char *crt_cuda_last_error(const crt_cuda_ctx *ctx);
-/* run on a caller-provided CUDA stream (a cudaStream_t passed as void*); NULL = the context's own stream */
+/* run on a caller-provided CUDA stream (a cudaStream_t passed as void*); NULL = the context's own stream.
+ * The legacy default stream is cudaStreamLegacy ((void*)1), not NULL. */
 int crt_cuda_set_stream(crt_cuda_ctx *ctx, void *stream);
 
 /* cudaMemcpyAsync of every array from (internally pinned) staging; replaces the implicit "scene is in RAM" */
