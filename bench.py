@@ -190,7 +190,8 @@ def run_ours(args):
         orbit = scenes.orbit_cameras(list(flat.camera.position), list(flat.camera.rotation), center, 240)
     frame_parallel = orbit is not None  # animation: whole frames per rank, no exchange
     band_rows = 8
-    common = dict(max_ray_depth=depth, traversal=crt.TRAVERSAL_KD)
+    pipeline = {"auto": crt.PIPELINE_AUTO, "mega": crt.PIPELINE_MEGAKERNEL, "wavefront": crt.PIPELINE_WAVEFRONT}[args.pipeline]
+    common = dict(max_ray_depth=depth, traversal=crt.TRAVERSAL_KD, pipeline=pipeline)
     part = dict(rank=0, world=1) if frame_parallel else dict(rank=rank, world=world, band_rows=band_rows)
     params = crt.default_params(**common, **part)
 
@@ -315,7 +316,7 @@ def run_ours(args):
     line = {"metric": "Mrays/s (primary+secondary)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if frame_parallel else "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "traversal": "kd", "partition": ("frames round-robin" if frame_parallel else f"row bands of {band_rows}, gather of u8 rgb to rank 0") if world > 1 else "single GPU",
+            "config": {"workload": desc, "traversal": "kd", "pipeline": args.pipeline, "partition": ("frames round-robin" if frame_parallel else f"row bands of {band_rows}, gather of u8 rgb to rank 0") if world > 1 else "single GPU",
                        "l2": "256 MiB flush between timed steps", "rays_per_step": job_rays_per_step, "scene_load_s": t_load, "scene_upload_s": t_upload,
                        "scene_bytes": int(flat.n_triangles * 64 + flat.n_nodes * 48 + flat.n_refs * 4)},
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
@@ -335,6 +336,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

@@ -37,7 +37,8 @@ struct WfBuffers {
 
 struct WavefrontState {
     WfBuffers b{};
-    size_t node_capacity = 0; // allocated entries of hit/rec/alb/col
+    size_t node_capacity = 0; // allocated entries of hit
+    size_t tree_capacity = 0; // allocated entries of rec/alb/col
     size_t ray_capacity = 0;  // allocated entries of ray_o/ray_d
     size_t pend_capacity = 0;
     int sm_count = 0;
@@ -336,19 +337,22 @@ inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
     const size_t cap = secondary ? size_t(double(P) * w.grow) + 1024 : 0;
     const size_t nodes = size_t(P) + cap;
     if (nodes > w.node_capacity) {
-        cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col);
-        w.b.hit = nullptr, w.b.rec = nullptr, w.b.alb = nullptr, w.b.col = nullptr, w.node_capacity = 0;
+        cudaFree(w.b.hit);
+        w.b.hit = nullptr, w.node_capacity = 0;
         if ((e = cudaMalloc(&w.b.hit, nodes * sizeof(float2))) != cudaSuccess)
             return e;
-        if (secondary) {
-            if ((e = cudaMalloc(&w.b.rec, nodes * sizeof(int4))) != cudaSuccess)
-                return e;
-            if ((e = cudaMalloc(&w.b.alb, nodes * sizeof(float4))) != cudaSuccess)
-                return e;
-            if ((e = cudaMalloc(&w.b.col, nodes * sizeof(float4))) != cudaSuccess)
-                return e;
-        }
         w.node_capacity = nodes;
+    }
+    if (secondary && nodes > w.tree_capacity) { // rec/alb/col exist only once a scene with secondary rays was seen
+        cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col);
+        w.b.rec = nullptr, w.b.alb = nullptr, w.b.col = nullptr, w.tree_capacity = 0;
+        if ((e = cudaMalloc(&w.b.rec, nodes * sizeof(int4))) != cudaSuccess)
+            return e;
+        if ((e = cudaMalloc(&w.b.alb, nodes * sizeof(float4))) != cudaSuccess)
+            return e;
+        if ((e = cudaMalloc(&w.b.col, nodes * sizeof(float4))) != cudaSuccess)
+            return e;
+        w.tree_capacity = nodes;
     }
     if (cap > w.ray_capacity) {
         cudaFree(w.b.ray_o), cudaFree(w.b.ray_d);

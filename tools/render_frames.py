@@ -1,0 +1,29 @@
+#!/usr/bin/env python
+"""Render a few frames of a bench workload through the C ABI (no torch): the short command ncu wraps.
+usage: python tools/render_frames.py <workload> [frames] [pipeline auto|mega|wavefront] [traversal kd|literal] [stats 0|1]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import bench  # noqa: E402
+import __graft_entry__ as entry  # noqa: E402
+
+workload = sys.argv[1] if len(sys.argv) > 1 else "c4"
+frames = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+pipeline = sys.argv[3] if len(sys.argv) > 3 else "auto"
+traversal = sys.argv[4] if len(sys.argv) > 4 else "kd"
+stats = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+crt = entry.load_package()
+desc, W, H, depth, _ = bench.WORKLOADS[workload]
+text, root = bench.scene_text(workload)
+scene = crt.Scene.load_json(text, root)
+r = crt.Renderer(0)
+flat = r.upload(scene)
+p = crt.default_params(max_ray_depth=depth, collect_stats=stats,
+                       pipeline={"auto": 0, "mega": 1, "wavefront": 2}[pipeline], traversal={"kd": 1, "literal": 0}[traversal])
+for i in range(frames):
+    _, _, st = r.render(p, want_rgb=False, want_rgb8=False)
+    print(workload, pipeline, traversal, "frame", i, {k: v for k, v in st.items() if v and k != "pad"})
+r.close()
