@@ -119,6 +119,23 @@ __device__ __forceinline__ bool triangle_test(const float4 &A, const float4 &B, 
     return false;
 }
 
+// Same decisions and the same t as triangle_test, evaluated without branches (every lane of a warp runs the same
+// instruction stream; rejected candidates simply yield false).  The arithmetic of each quantity is the same
+// operation sequence, so accept/reject and t are bit-identical to the branching form: a quantity that the
+// branching form would not have computed (e.g. t for rn ~ 0) only feeds comparisons whose result is masked.
+__device__ __forceinline__ bool triangle_test_flat(const float4 &A, const float4 &B, const float4 &C, bool cull, V3 o, V3 d, float &t_out) {
+    const V3 v0 = xyz(A), v1 = xyz(B), v2 = xyz(C), N = mk(A.w, B.w, C.w);
+    const float rn = dot(N, d);
+    const float dist = dot(N, v0 - o);
+    const float t = dist / rn;
+    const V3 P = o + d * t;
+    const V3 e0 = v1 - v0, e1 = v2 - v1, e2 = v0 - v2;
+    const float s0 = dot(N, cross(e0, P - v0)), s1 = dot(N, cross(e1, P - v1)), s2 = dot(N, cross(e2, P - v2));
+    const bool ok = !(fabsf(rn) < 1e-6f) & !(!(dist < 0.0f) & cull) & !(t < 0.0f) & (s0 >= 0.0f) & (s1 >= 0.0f) & (s2 >= 0.0f);
+    t_out = t;
+    return ok;
+}
+
 // ------------------------------------------------------------------------------------------------ box (a3)
 // ray_intersect_aabb_p, src/core/crt_intersection.cpp:14-45: six face planes, min faces first, x,y,z order,
 // hit point must lie inside the face rectangle (inclusive).  NOT a slab test; kept literal for verification.
