@@ -503,4 +503,16 @@ int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size
     return fail(ctx, CRT_ERR_INVALID, "crt_cuda_encode_ppm: not built yet");
 }
 
+#ifdef CRT_DEBUG_TAIL
+int crt_debug_tail(unsigned long long *out /* 16*40 */, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, crtdev::g_tail, sizeof(unsigned long long) * 16 * 40);
+    if (reset) {
+        static unsigned long long zero[16 * 40];
+        cudaMemcpyToSymbol(crtdev::g_tail, zero, sizeof zero);
+    }
+    return 0;
+}
+#endif
+
 } // extern "C"

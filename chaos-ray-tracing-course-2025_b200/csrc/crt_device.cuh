@@ -289,6 +289,55 @@ struct KdWalker {
             ++cn->node_tests;
     }
 
+    // ONE node of the walk, given the already loaded node `n` of `node`: returns true when `n` is a leaf (the caller
+    // tests n.y .. n.y + n.z and then calls pop); otherwise moves to the next node (pushing the far child, or
+    // popping when a child is absent), leaving node = -1 when the walk has run out of nodes.
+    template <bool STATS>
+    __device__ __forceinline__ bool step(const int4 n, Counters *cn) {
+        if (n.w == 3)
+            return true;
+        const int axis = n.w;
+        const float split = __int_as_float(n.x);
+        const float oa = pick(o, axis), da = pick(d, axis), ia = pick(inv, axis);
+        const bool below = (oa < split) || (oa == split && da <= 0.0f);
+        const int near = below ? n.y : n.z, far = below ? n.z : n.y;
+        const float tp = (split - oa) * ia;
+        const float slack = fabsf(tp) * 1e-5f + 1e-6f;
+        int next;
+        bool push = false;
+        float push_min = tp;
+        if (tp != tp) { // origin on the plane and direction parallel to it: the ray lies in both boxes
+            push = far >= 0 && near >= 0;
+            push_min = tmin;
+            next = near >= 0 ? near : far;
+        } else if (tp <= 0.0f || tp > tmax + slack) {
+            next = near;
+        } else if (tp < tmin - slack) {
+            next = far;
+        } else if (far >= 0 && near >= 0) {
+            push = true;
+            next = near;
+        } else if (far >= 0) {
+            next = far;
+            tmin = fmaxf(tmin, tp);
+        } else {
+            next = near;
+        }
+        if (push) {
+            snode[sp] = far, smin[sp] = push_min, smax[sp] = tmax, ++sp;
+            if (tp == tp)
+                tmax = fminf(tmax, tp);
+        }
+        if (next >= 0) {
+            node = next;
+            if (STATS)
+                ++cn->node_tests;
+        } else {
+            pop<STATS>(cn);
+        }
+        return false;
+    }
+
     // descend from `node` to the next leaf (pushing far children); returns the leaf's kd node, or w = -1 if the
     // walk ran out of nodes on the way
     template <bool STATS>

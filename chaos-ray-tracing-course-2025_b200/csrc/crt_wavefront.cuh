@@ -91,6 +91,12 @@ struct __align__(16) TraceWarpShared {
     uint2 ring[kRing];                 // candidates: {leaf reference (triangle | cull bit), owner lane}
 };
 
+#ifdef CRT_DEBUG_TAIL
+// debugging aid (never in the product build): per level, the longest walk (in rounds of the trace loop), the sum of
+// all rounds, and a log2 histogram of rounds per ray
+__device__ unsigned long long g_tail[16][40];
+#endif
+
 constexpr unsigned long long kNoHitKey = (0x7f800000ull << 32) | 0xffffffffull; // t = +inf, tri = -1
 
 template <bool STATS>
@@ -125,6 +131,10 @@ __global__ void __launch_bounds__(kTraceBlock) k_wf_trace(const __grid_constant_
     w.node = -1;
     int my = -1; // index of my ray within the level, -1 = idle
     bool live = false; // my ray entered the root box: its best lives in ws.best[lane]
+    int leaf_first = 0, leaf_count = 0; // leaf my walk has reached and that awaits the next test phase
+#ifdef CRT_DEBUG_TAIL
+    unsigned rounds = 0;
+#endif
     bool exhausted = false;
     for (;;) {
         // ---- refill idle lanes
@@ -180,74 +190,82 @@ __global__ void __launch_bounds__(kTraceBlock) k_wf_trace(const __grid_constant_
                 break;
             continue;
         }
+#ifdef CRT_DEBUG_TAIL
+        if (my >= 0)
+            ++rounds;
+#endif
         if (TRAV == CRT_TRAVERSAL_KD) {
-            // ---- 1. descend
-            const bool walking = my >= 0 && !w.done();
-            int leaf_first = 0, leaf_count = 0;
-            if (walking) {
-                const int4 leaf = w.descend<STATS>(S, &cn);
-                if (leaf.w >= 0)
-                    leaf_first = leaf.y, leaf_count = leaf.z;
-            }
-            __syncwarp();
-            // ---- 2. gather: exclusive prefix of the leaf sizes
-            int incl = leaf_count;
+            // ---- 1. walkers issue the load of their next node now; it is consumed after the leaf phase
+            const bool walking = my >= 0 && !w.done() && leaf_count == 0;
+            int4 n = make_int4(0, 0, 0, 0);
+            if (walking)
+                n = __ldg(&S.kd_nodes[w.node]);
+            // ---- 2. gather + 3. test: lanes that reached a leaf in the previous round
+            if (__any_sync(0xffffffffu, leaf_count > 0)) {
+                int incl = leaf_count;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (int(lane) >= o)
-                    incl += v;
-            }
-            const int items = __shfl_sync(0xffffffffu, incl, 31);
-            const int excl = incl - leaf_count;
-            int head = 0, fill = 0;
-            for (int base_item = 0; base_item < items; base_item += 32) {
-                const int item = base_item + int(lane);
-                // owner = last lane whose exclusive prefix is <= item (binary search over the lanes' registers)
-                int owner = 0;
-#pragma unroll
-                for (int step = 16; step > 0; step >>= 1) {
-                    const int probe = __shfl_sync(0xffffffffu, excl, owner + step);
-                    if (probe <= item)
-                        owner += step;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (int(lane) >= o)
+                        incl += v;
                 }
-                // lanes with equal prefixes (empty leaves) resolve to the LAST of them; an empty owner has no item
-                // of its own, and every item below `items` belongs to a lane with a non-empty leaf, which is the
-                // last lane of its run of equal prefixes.
-                const int owner_first = __shfl_sync(0xffffffffu, leaf_first, owner);
-                const int owner_excl = __shfl_sync(0xffffffffu, excl, owner);
-                bool keep = false;
-                uint32_t ref = 0;
-                if (item < items) {
-                    ref = __ldg(&S.refs[owner_first + (item - owner_excl)]);
-                    const int tri = int(ref & 0x7FFFFFFFu);
-                    int *slot = &ws.mailbox[(uint32_t(tri) * 0x9E3779B1u) >> 28][owner];
-                    keep = *slot != tri;
+                const int items = __shfl_sync(0xffffffffu, incl, 31);
+                const int excl = incl - leaf_count;
+                int head = 0, fill = 0;
+                for (int base_item = 0; base_item < items; base_item += 32) {
+                    const int item = base_item + int(lane);
+                    // owner = last lane whose exclusive prefix is <= item (binary search over the lanes' registers);
+                    // lanes with equal prefixes have empty leaves except the last of the run, which owns the item
+                    int owner = 0;
+#pragma unroll
+                    for (int stride = 16; stride > 0; stride >>= 1) {
+                        const int probe = __shfl_sync(0xffffffffu, excl, owner + stride);
+                        if (probe <= item)
+                            owner += stride;
+                    }
+                    const int owner_first = __shfl_sync(0xffffffffu, leaf_first, owner);
+                    const int owner_excl = __shfl_sync(0xffffffffu, excl, owner);
+                    bool keep = false;
+                    uint32_t ref = 0;
+                    if (item < items) {
+                        ref = __ldg(&S.refs[owner_first + (item - owner_excl)]);
+                        const int tri = int(ref & 0x7FFFFFFFu);
+                        int *slot = &ws.mailbox[(uint32_t(tri) * 0x9E3779B1u) >> 28][owner];
+                        keep = *slot != tri;
+                        if (keep)
+                            *slot = tri;
+                    }
+                    const unsigned kmask = __ballot_sync(0xffffffffu, keep);
                     if (keep)
-                        *slot = tri;
+                        ws.ring[(head + fill + __popc(kmask & lt_mask)) & (kRing - 1)] = make_uint2(ref, unsigned(owner));
+                    fill += __popc(kmask);
+                    __syncwarp();
+                    if (fill >= 32) {
+                        trace_test_ring<STATS>(S, ws, head, 32, lane, cn);
+                        head = (head + 32) & (kRing - 1);
+                        fill -= 32;
+                        __syncwarp();
+                    }
                 }
-                const unsigned kmask = __ballot_sync(0xffffffffu, keep);
-                if (keep)
-                    ws.ring[(head + fill + __popc(kmask & lt_mask)) & (kRing - 1)] = make_uint2(ref, unsigned(owner));
-                fill += __popc(kmask);
-                __syncwarp();
-                if (fill >= 32) {
-                    trace_test_ring<STATS>(S, ws, head, 32, lane, cn);
-                    head = (head + 32) & (kRing - 1);
-                    fill -= 32;
+                if (fill > 0) {
+                    trace_test_ring<STATS>(S, ws, head, fill, lane, cn);
                     __syncwarp();
                 }
+                // ---- 4. pop: the leaf's owner reads its best back and prunes its stack
+                if (leaf_count > 0) {
+                    const unsigned long long key = ws.best[lane];
+                    w.best.t = __uint_as_float(unsigned(key >> 32));
+                    w.best.tri = int(unsigned(key & 0xffffffffull));
+                    w.pop<STATS>(&cn);
+                    leaf_count = 0;
+                }
             }
-            if (fill > 0) {
-                trace_test_ring<STATS>(S, ws, head, fill, lane, cn);
-                __syncwarp();
-            }
-            // ---- 4. pop
-            if (walking && !w.done()) {
-                const unsigned long long key = ws.best[lane];
-                w.best.t = __uint_as_float(unsigned(key >> 32));
-                w.best.tri = int(unsigned(key & 0xffffffffull));
-                w.pop<STATS>(&cn);
+            // ---- 1'. one node step for the lanes that loaded a node above
+            if (walking && w.step<STATS>(n, &cn)) { // a leaf: tested next round
+                if (n.z > 0)
+                    leaf_first = n.y, leaf_count = n.z;
+                else
+                    w.pop<STATS>(&cn);
             }
         }
         if (my >= 0 && w.done()) {
@@ -259,6 +277,12 @@ __global__ void __launch_bounds__(kTraceBlock) k_wf_trace(const __grid_constant_
                 h.tri = int(unsigned(key & 0xffffffffull));
             }
             b.hit[node_id] = make_float2(h.t, __int_as_float(h.tri));
+#ifdef CRT_DEBUG_TAIL
+            atomicMax(&g_tail[level][0], (unsigned long long)rounds);
+            atomicAdd(&g_tail[level][1], (unsigned long long)rounds);
+            atomicAdd(&g_tail[level][2 + (rounds ? 32 - __clz(rounds) : 0)], 1ull);
+            rounds = 0;
+#endif
             my = -1;
         }
     }
