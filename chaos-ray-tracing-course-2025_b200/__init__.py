@@ -14,7 +14,8 @@ from dataclasses import dataclass
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libcrt_b200.so")
+# CRT_B200_LIB: a differently tuned build of the SAME library (kernel parameter sweeps); never a different backend
+LIB_PATH = os.environ.get("CRT_B200_LIB") or os.path.join(_HERE, "lib", "libcrt_b200.so")
 
 CRT_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_IO, ERR_PARSE, ERR_NO_DEVICE = -1, -2, -3, -4, -5

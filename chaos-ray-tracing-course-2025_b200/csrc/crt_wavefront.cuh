@@ -64,231 +64,9 @@ __device__ __forceinline__ bool slot_pixel(const WfBuffers &b, const DScene &S, 
 }
 
 // ------------------------------------------------------------------------------------------------ TRACE
-// Persistent warps over the level's ray queue.  Each lane owns one ray at a time; when fewer than kRefillBelow lanes
-// still have work the idle lanes take the next rays of the queue (one atomicAdd per warp, ballot + popc offsets).
-//
-// The walk is WARP-SYNCHRONOUS (ncu of the first version, profiles/r1c_*: per-lane leaf loops with early-outs ran
-// with 2.4 of 32 threads active per instruction and the triangle test was 75 % of all issued instructions):
-//   1. DESCEND  every lane with a live ray walks its k-d interval down to its next leaf (nodes are 16 B loads);
-//   2. GATHER   the (ray, leaf reference) pairs of all 32 lanes form one list (shfl prefix sum of the leaf sizes);
-//               the list is consumed 32 entries at a time by ALL lanes regardless of which ray an entry belongs to:
-//               leaf reference load -> per-ray mailbox filter -> ballot compaction into a 64-entry ring in shared
-//               memory;
-//   3. TEST     whenever the ring holds 32 candidates, every lane runs one branch-free triangle test (ray fetched
-//               from the owner's shared-memory slot, triangle = 3 float4 loads) and merges a hit into the owner's
-//               best with a 64-bit shared-memory atomicMin on (t bits << 32 | triangle index) -- which is exactly
-//               the reference's winner rule "closest, ties to the first in visiting order = lowest parse index";
-//   4. POP      every lane reads its best back, prunes its stack and either continues or retires its ray.
-constexpr int kTraceBlock = 128;
-constexpr int kTraceWarps = kTraceBlock / 32;
-constexpr int kRefillBelow = 25;
-constexpr int kRing = 64;
-
-struct __align__(16) TraceWarpShared {
-    float ray[6][32];                  // origin xyz, direction xyz of each lane's ray
-    unsigned long long best[32];       // (float bits of t) << 32 | triangle index; t >= 0 so the order is numeric
-    int mailbox[kMailboxSlots][32];    // per-ray direct-mapped table of triangles already tested
-    uint2 ring[kRing];                 // candidates: {leaf reference (triangle | cull bit), owner lane}
-};
-
-#ifdef CRT_DEBUG_TAIL
-// debugging aid (never in the product build): per level, the longest walk (in rounds of the trace loop), the sum of
-// all rounds, and a log2 histogram of rounds per ray
-__device__ unsigned long long g_tail[16][40];
-#endif
-
-constexpr unsigned long long kNoHitKey = (0x7f800000ull << 32) | 0xffffffffull; // t = +inf, tri = -1
-
-template <bool STATS>
-__device__ __forceinline__ void trace_test_ring(const DScene &S, TraceWarpShared &ws, int head, int n, unsigned lane, Counters &cn) {
-    if (int(lane) < n) {
-        const uint2 e = ws.ring[(head + int(lane)) & (kRing - 1)];
-        const int tri = int(e.x & 0x7FFFFFFFu), owner = int(e.y);
-        const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
-        const V3 o = mk(ws.ray[0][owner], ws.ray[1][owner], ws.ray[2][owner]), d = mk(ws.ray[3][owner], ws.ray[4][owner], ws.ray[5][owner]);
-        if (STATS)
-            ++cn.tri_tests;
-        float t;
-        if (triangle_test_flat(A, B, C, (e.x >> 31) != 0, o, d, t)) {
-            t = t + 0.0f; // -0 -> +0 so the bit pattern orders like the value
-            atomicMin(&ws.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(unsigned)tri);
-        }
-    }
-}
-
-template <int TRAV, bool STATS>
-__global__ void __launch_bounds__(kTraceBlock) k_wf_trace(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
-                                                          const __grid_constant__ WfBuffers b, int level, Counters *__restrict__ counters) {
-    __shared__ TraceWarpShared shared[kTraceWarps];
-    TraceWarpShared &ws = shared[threadIdx.x >> 5];
-    WfCtl *ctl = b.ctl;
-    const int total = level == 0 ? b.P : ctl->count[level];
-    const int start = level == 0 ? 0 : level_start(ctl, level);
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    Counters cn{};
-    KdWalker w;
-    w.node = -1;
-    int my = -1; // index of my ray within the level, -1 = idle
-    bool live = false; // my ray entered the root box: its best lives in ws.best[lane]
-    int leaf_first = 0, leaf_count = 0; // leaf my walk has reached and that awaits the next test phase
-#ifdef CRT_DEBUG_TAIL
-    unsigned rounds = 0;
-#endif
-    bool exhausted = false;
-    for (;;) {
-        // ---- refill idle lanes
-        const unsigned busy = __ballot_sync(0xffffffffu, my >= 0);
-        if (!exhausted && __popc(busy) < kRefillBelow) {
-            const unsigned idle = ~busy;
-            int base = 0;
-            if (lane == 0)
-                base = atomicAdd(&ctl->fetch[level], __popc(idle));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (base + __popc(idle) >= total)
-                exhausted = true;
-            if (my < 0) {
-                const int i = base + __popc(idle & lt_mask);
-                if (i < total) {
-                    Ray r;
-                    bool have = true;
-                    if (level == 0) {
-                        int x, ly;
-                        have = slot_pixel(b, S, P, i, x, ly);
-                        if (have)
-                            r = generate_ray(S.cam, x, global_row(P, ly));
-                    } else {
-                        r = Ray{ xyz(b.ray_o[start + i]), xyz(b.ray_d[start + i]) };
-                    }
-                    if (have) {
-                        if (STATS) {
-                            ++cn.rays;
-                            ++cn.rays_by_depth[level];
-                        }
-                        my = i;
-                        if (TRAV == CRT_TRAVERSAL_KD) {
-                            live = w.init<STATS>(S, r, &cn);
-                            if (live) {
-                                ws.ray[0][lane] = r.o.x, ws.ray[1][lane] = r.o.y, ws.ray[2][lane] = r.o.z;
-                                ws.ray[3][lane] = r.d.x, ws.ray[4][lane] = r.d.y, ws.ray[5][lane] = r.d.z;
-                                ws.best[lane] = kNoHitKey;
-#pragma unroll
-                                for (int k = 0; k < kMailboxSlots; ++k)
-                                    ws.mailbox[k][lane] = -1;
-                            }
-                        } else {
-                            // verification traversal: run the reference-order walk to completion right here
-                            w.best = trace_literal<STATS>(S, r, &cn);
-                            w.node = -1;
-                        }
-                    }
-                }
-            }
-        }
-        if (__ballot_sync(0xffffffffu, my >= 0) == 0u) {
-            if (exhausted)
-                break;
-            continue;
-        }
-#ifdef CRT_DEBUG_TAIL
-        if (my >= 0)
-            ++rounds;
-#endif
-        if (TRAV == CRT_TRAVERSAL_KD) {
-            // ---- 1. walkers issue the load of their next node now; it is consumed after the leaf phase
-            const bool walking = my >= 0 && !w.done() && leaf_count == 0;
-            int4 n = make_int4(0, 0, 0, 0);
-            if (walking)
-                n = __ldg(&S.kd_nodes[w.node]);
-            // ---- 2. gather + 3. test: lanes that reached a leaf in the previous round
-            if (__any_sync(0xffffffffu, leaf_count > 0)) {
-                int incl = leaf_count;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (int(lane) >= o)
-                        incl += v;
-                }
-                const int items = __shfl_sync(0xffffffffu, incl, 31);
-                const int excl = incl - leaf_count;
-                int head = 0, fill = 0;
-                for (int base_item = 0; base_item < items; base_item += 32) {
-                    const int item = base_item + int(lane);
-                    // owner = last lane whose exclusive prefix is <= item (binary search over the lanes' registers);
-                    // lanes with equal prefixes have empty leaves except the last of the run, which owns the item
-                    int owner = 0;
-#pragma unroll
-                    for (int stride = 16; stride > 0; stride >>= 1) {
-                        const int probe = __shfl_sync(0xffffffffu, excl, owner + stride);
-                        if (probe <= item)
-                            owner += stride;
-                    }
-                    const int owner_first = __shfl_sync(0xffffffffu, leaf_first, owner);
-                    const int owner_excl = __shfl_sync(0xffffffffu, excl, owner);
-                    bool keep = false;
-                    uint32_t ref = 0;
-                    if (item < items) {
-                        ref = __ldg(&S.refs[owner_first + (item - owner_excl)]);
-                        const int tri = int(ref & 0x7FFFFFFFu);
-                        int *slot = &ws.mailbox[(uint32_t(tri) * 0x9E3779B1u) >> 28][owner];
-                        keep = *slot != tri;
-                        if (keep)
-                            *slot = tri;
-                    }
-                    const unsigned kmask = __ballot_sync(0xffffffffu, keep);
-                    if (keep)
-                        ws.ring[(head + fill + __popc(kmask & lt_mask)) & (kRing - 1)] = make_uint2(ref, unsigned(owner));
-                    fill += __popc(kmask);
-                    __syncwarp();
-                    if (fill >= 32) {
-                        trace_test_ring<STATS>(S, ws, head, 32, lane, cn);
-                        head = (head + 32) & (kRing - 1);
-                        fill -= 32;
-                        __syncwarp();
-                    }
-                }
-                if (fill > 0) {
-                    trace_test_ring<STATS>(S, ws, head, fill, lane, cn);
-                    __syncwarp();
-                }
-                // ---- 4. pop: the leaf's owner reads its best back and prunes its stack
-                if (leaf_count > 0) {
-                    const unsigned long long key = ws.best[lane];
-                    w.best.t = __uint_as_float(unsigned(key >> 32));
-                    w.best.tri = int(unsigned(key & 0xffffffffull));
-                    w.pop<STATS>(&cn);
-                    leaf_count = 0;
-                }
-            }
-            // ---- 1'. one node step for the lanes that loaded a node above
-            if (walking && w.step<STATS>(n, &cn)) { // a leaf: tested next round
-                if (n.z > 0)
-                    leaf_first = n.y, leaf_count = n.z;
-                else
-                    w.pop<STATS>(&cn);
-            }
-        }
-        if (my >= 0 && w.done()) {
-            const int node_id = level == 0 ? my : b.P + start + my;
-            Hit h = w.best; // literal walk, or a ray that never entered the root box
-            if (TRAV == CRT_TRAVERSAL_KD && live) {
-                const unsigned long long key = ws.best[lane];
-                h.t = __uint_as_float(unsigned(key >> 32));
-                h.tri = int(unsigned(key & 0xffffffffull));
-            }
-            b.hit[node_id] = make_float2(h.t, __int_as_float(h.tri));
-#ifdef CRT_DEBUG_TAIL
-            atomicMax(&g_tail[level][0], (unsigned long long)rounds);
-            atomicAdd(&g_tail[level][1], (unsigned long long)rounds);
-            atomicAdd(&g_tail[level][2 + (rounds ? 32 - __clz(rounds) : 0)], 1ull);
-            rounds = 0;
-#endif
-            my = -1;
-        }
-    }
-    if (STATS)
-        flush_counters(cn, counters);
-}
+} // namespace crtdev
+#include "crt_trace.cuh"
+namespace crtdev {
 
 // ------------------------------------------------------------------------------------------------ SHADE
 __device__ __forceinline__ void write_pixel(const DScene &S, float *__restrict__ rgb, uint8_t *__restrict__ rgb8, int x, int ly, V3 c) {
