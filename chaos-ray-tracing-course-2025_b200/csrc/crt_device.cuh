@@ -217,6 +217,44 @@ __device__ __forceinline__ Hit trace_literal(const DScene &S, const Ray &r, Coun
 // per triangle in the 1 M-triangle scene), so consecutive leaves along a ray hold mostly the same triangles.
 // A small direct-mapped per-ray table of already-tested triangle ids (shared memory, [slot][thread] layout =
 // conflict-free) skips the repeats; a repeat test would return the same t, so results are unchanged.
+// Entry of a ray into the root box (what KdWalker::init computes), as a value: used by the kernels that CREATE rays
+// (primary ray generation, the shade stage) so that the trace stage starts a walk from a ready-made record.
+struct RaySetup {
+    V3 inv;
+    float tmin, tmax;
+    bool live; // false: NaN direction or the ray misses the root box -- nothing to walk
+};
+__device__ __forceinline__ RaySetup ray_setup(const DScene &S, const Ray &r) {
+    RaySetup q;
+    const V3 o = r.o, d = r.d;
+    q.inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    q.tmin = 0.0f, q.tmax = kInf;
+    q.live = d.x == d.x && d.y == d.y && d.z == d.z; // NaN direction (refraction at normal incidence, crt_vector.cpp:11-27)
+    const float lx = S.root_min[0], ly = S.root_min[1], lz = S.root_min[2], hx = S.root_max[0], hy = S.root_max[1], hz = S.root_max[2];
+    if (d.x != 0.0f) {
+        const float a = (lx - o.x) * q.inv.x, b = (hx - o.x) * q.inv.x;
+        q.tmin = fmaxf(q.tmin, fminf(a, b));
+        q.tmax = fminf(q.tmax, fmaxf(a, b));
+    } else if (o.x < lx || o.x > hx)
+        q.live = false;
+    if (d.y != 0.0f) {
+        const float a = (ly - o.y) * q.inv.y, b = (hy - o.y) * q.inv.y;
+        q.tmin = fmaxf(q.tmin, fminf(a, b));
+        q.tmax = fminf(q.tmax, fmaxf(a, b));
+    } else if (o.y < ly || o.y > hy)
+        q.live = false;
+    if (d.z != 0.0f) {
+        const float a = (lz - o.z) * q.inv.z, b = (hz - o.z) * q.inv.z;
+        q.tmin = fmaxf(q.tmin, fminf(a, b));
+        q.tmax = fminf(q.tmax, fmaxf(a, b));
+    } else if (o.z < lz || o.z > hz)
+        q.live = false;
+    q.tmax = q.tmax + (fabsf(q.tmax) * 1e-5f + 1e-6f);
+    if (!(q.tmin <= q.tmax))
+        q.live = false;
+    return q;
+}
+
 constexpr int kMailboxSlots = 16;
 
 struct KdWalker {

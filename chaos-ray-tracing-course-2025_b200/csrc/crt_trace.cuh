@@ -40,8 +40,11 @@ constexpr int kTraceWarps = kTraceBlock / 32;
 #ifndef CRT_WIN
 #define CRT_WIN 8
 #endif
+#ifndef CRT_TEST_FIRST
+#define CRT_TEST_FIRST 1
+#endif
 #ifndef CRT_MINBLOCKS
-#define CRT_MINBLOCKS 1
+#define CRT_MINBLOCKS 7
 #endif
 constexpr int kRefillBelow = CRT_REFILL;
 constexpr int kRing = 128;      // candidates: < 32 carried over + one round's gather, drained 32 at a time
@@ -72,55 +75,28 @@ struct TraceWalker {
     int sp, lo, flagged;
     uint2 spill[kStack];
 
-    template <bool STATS>
-    __device__ __forceinline__ bool init(const DScene &S, TraceWarpShared &ws, unsigned lane, const Ray &r, Counters &cn) {
-        node = -1, sp = 0, lo = 0, flagged = 0;
-        const V3 o = r.o, d = r.d;
-        if (!(d.x == d.x && d.y == d.y && d.z == d.z))
-            return false; // NaN direction (refraction at normal incidence, crt_vector.cpp:11-27): every compare is false
-        const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-        tmin = 0.0f, tmax = kInf;
-        const float lx = S.root_min[0], ly = S.root_min[1], lz = S.root_min[2], hx = S.root_max[0], hy = S.root_max[1], hz = S.root_max[2];
-        if (d.x != 0.0f) {
-            const float a = (lx - o.x) * inv.x, b = (hx - o.x) * inv.x;
-            tmin = fmaxf(tmin, fminf(a, b));
-            tmax = fminf(tmax, fmaxf(a, b));
-        } else if (o.x < lx || o.x > hx)
-            return false;
-        if (d.y != 0.0f) {
-            const float a = (ly - o.y) * inv.y, b = (hy - o.y) * inv.y;
-            tmin = fmaxf(tmin, fminf(a, b));
-            tmax = fminf(tmax, fmaxf(a, b));
-        } else if (o.y < ly || o.y > hy)
-            return false;
-        if (d.z != 0.0f) {
-            const float a = (lz - o.z) * inv.z, b = (hz - o.z) * inv.z;
-            tmin = fmaxf(tmin, fminf(a, b));
-            tmax = fminf(tmax, fmaxf(a, b));
-        } else if (o.z < lz || o.z > hz)
-            return false;
-        if (STATS)
-            ++cn.node_tests;
-        tmax = tmax + (fabsf(tmax) * 1e-5f + 1e-6f);
-        if (tmin > tmax)
-            return false;
-        root_tmax = tmax;
+    // start a walk from a ray record (entry/exit of the root box and 1/direction come with the record)
+    __device__ __forceinline__ void start(TraceWarpShared &ws, unsigned lane, V3 o, V3 d, V3 inv, float t_enter, float t_exit) {
+        sp = 0, lo = 0, flagged = 0;
+        tmin = t_enter, tmax = t_exit, root_tmax = t_exit;
         node = 0;
         ws.ray[0][lane] = o.x, ws.ray[1][lane] = o.y, ws.ray[2][lane] = o.z;
         ws.ray[3][lane] = d.x, ws.ray[4][lane] = d.y, ws.ray[5][lane] = d.z;
         ws.ray[6][lane] = inv.x, ws.ray[7][lane] = inv.y, ws.ray[8][lane] = inv.z;
-        return true;
     }
 
     __device__ __forceinline__ bool done() const { return node < 0; }
 
-    __device__ __forceinline__ void push(TraceWarpShared &ws, unsigned lane, uint32_t tagged_node, float entry) {
-        if (sp - lo == kWin) {
+    // the store happens whether or not anything is pushed (slot sp is free), only the count moves: no branch per push
+    __device__ __forceinline__ void push_if(TraceWarpShared &ws, unsigned lane, bool doit, uint32_t tagged_node, float entry) {
+        const bool full = sp - lo == kWin;
+        if (doit & full) { // window full (rare): the oldest entry goes to local memory
             spill[lo] = ws.stack[lo & (kWin - 1)][lane];
             ++lo;
         }
-        ws.stack[sp & (kWin - 1)][lane] = make_uint2(tagged_node, __float_as_uint(entry));
-        ++sp;
+        if (doit | !full) // a full window's slot sp IS the oldest entry: leave it alone unless it was just spilled
+            ws.stack[sp & (kWin - 1)][lane] = make_uint2(tagged_node, __float_as_uint(entry));
+        sp += doit ? 1 : 0;
     }
 
     __device__ __forceinline__ uint2 entry_at(const TraceWarpShared &ws, unsigned lane, int i) const {
@@ -136,10 +112,15 @@ struct TraceWalker {
                 return;
             }
             --sp;
-            const uint2 e = entry_at(ws, lane, sp);
-            tmax = sp == 0 ? root_tmax : __uint_as_float(entry_at(ws, lane, sp - 1).y);
-            if (sp < lo)
-                lo = sp;
+            uint2 e = ws.stack[sp & (kWin - 1)][lane];
+            float below = __uint_as_float(ws.stack[(sp - 1) & (kWin - 1)][lane].y);
+            if (sp <= lo) { // rare: the entry or the one below it was spilled
+                if (sp < lo)
+                    e = spill[sp], lo = sp;
+                if (sp > 0)
+                    below = __uint_as_float(entry_at(ws, lane, sp - 1).y);
+            }
+            tmax = sp == 0 ? root_tmax : below;
             node = int(e.x & ~kFlagBit);
             if (e.x & kFlagBit) {
                 --flagged;
@@ -162,7 +143,9 @@ struct TraceWalker {
             ++cn.node_tests;
     }
 
-    // ONE node of the walk (KdWalker::step): true when `n` is a leaf
+    // ONE node of the walk: true when `n` is a leaf.  Same decisions as KdWalker::step, written as selects so that
+    // the lanes of a warp, which sit at unrelated nodes, share one instruction stream; only the push and the pop stay
+    // conditional.
     template <bool STATS>
     __device__ __forceinline__ bool step(TraceWarpShared &ws, unsigned lane, const int4 n, float best_t, Counters &cn) {
         if (n.w == 3)
@@ -170,38 +153,25 @@ struct TraceWalker {
         const int axis = n.w;
         const float split = __int_as_float(n.x);
         const float oa = ws.ray[axis][lane], da = ws.ray[3 + axis][lane], ia = ws.ray[6 + axis][lane];
-        const bool below = (oa < split) || (oa == split && da <= 0.0f);
+        const bool below = (oa < split) | ((oa == split) & (da <= 0.0f));
         const int near = below ? n.y : n.z, far = below ? n.z : n.y;
         const float tp = (split - oa) * ia;
         const float slack = fabsf(tp) * 1e-5f + 1e-6f;
-        int next;
-        if (tp != tp) { // origin on the plane and direction parallel to it: the ray lies in both boxes
-            if (far >= 0 && near >= 0) {
-                push(ws, lane, uint32_t(far) | kFlagBit, tmax);
-                ++flagged;
-            }
-            next = near >= 0 ? near : far;
-        } else if (tp <= 0.0f || tp > tmax + slack) {
-            next = near;
-        } else if (tp < tmin - slack) {
-            next = far;
-        } else if (far >= 0 && near >= 0) {
-            push(ws, lane, uint32_t(far), tp);
-            tmax = fminf(tmax, tp);
-            next = near;
-        } else if (far >= 0) {
-            next = far;
-            tmin = fmaxf(tmin, tp);
-        } else {
-            next = near;
-        }
-        if (next >= 0) {
-            node = next;
-            if (STATS)
-                ++cn.node_tests;
-        } else {
-            pop<STATS>(ws, lane, best_t, cn);
-        }
+        const bool in_plane = tp != tp; // origin on the plane and direction parallel to it: the ray lies in both boxes
+        const bool near_only = !in_plane & ((tp <= 0.0f) | (tp > tmax + slack));
+        const bool far_only = !in_plane & !near_only & (tp < tmin - slack);
+        const bool both = !near_only & !far_only;
+        const bool has_near = near >= 0, has_far = far >= 0;
+        const bool do_push = both & has_near & has_far;
+        const bool go_far = far_only | (both & !has_near);
+        const int next = go_far ? far : near;
+        push_if(ws, lane, do_push, uint32_t(far) | (in_plane ? kFlagBit : 0u), in_plane ? tmax : tp);
+        flagged += (do_push & in_plane) ? 1 : 0;
+        tmax = (do_push & !in_plane) ? fminf(tmax, tp) : tmax;
+        tmin = (both & !has_near & has_far & !in_plane) ? fmaxf(tmin, tp) : tmin;
+        node = next; // -1: the child is absent, the caller pops
+        if (STATS && next >= 0)
+            ++cn.node_tests;
         return false;
     }
 };
@@ -278,7 +248,7 @@ template <int TRAV, bool STATS>
 __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
                                                           const __grid_constant__ WfBuffers b, int level, Counters *__restrict__ counters) {
     WfCtl *ctl = b.ctl;
-    const int total = level == 0 ? b.P : ctl->count[level];
+    const int total = level == 0 ? (TRAV == CRT_TRAVERSAL_KD ? ctl->count[0] : b.P) : ctl->count[level];
     const int start = level == 0 ? 0 : level_start(ctl, level);
     Counters cn{};
     if (TRAV != CRT_TRAVERSAL_KD) {
@@ -295,6 +265,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
     TraceWalker w;
     w.node = -1, w.sp = 0, w.lo = 0, w.flagged = 0;
     int my = -1;                        // index of my ray within the level, -1 = idle
+    int node_id = 0;                    // where my ray's hit record goes
     bool live = false;                  // my ray entered the root box: its best lives in ws.best[lane]
     int leaf_first = 0, leaf_count = 0; // leaf reached in the previous round, gathered in this one
     // warp-uniform candidate bookkeeping: ring[head .. head+fill) are untested; `queued` / `tested` count candidates
@@ -319,30 +290,33 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
             if (my < 0) {
                 const int i = base + __popc(idle & lt_mask);
                 if (i < total) {
-                    Ray r;
-                    bool have = true;
+                    V3 o, d, inv;
+                    float t_enter, t_exit;
                     if (level == 0) {
-                        int x, ly;
-                        have = slot_pixel(b, S, P, i, x, ly);
-                        if (have)
-                            r = generate_ray(S.cam, x, global_row(P, ly));
+                        const float4 rd = b.ray0_d[i], ri = b.ray0_i[i];
+                        node_id = b.ray0_slot[i];
+                        o = mk(S.cam.position[0], S.cam.position[1], S.cam.position[2]);
+                        d = xyz(rd), inv = xyz(ri), t_enter = rd.w, t_exit = ri.w;
                     } else {
-                        r = Ray{ xyz(b.ray_o[start + i]), xyz(b.ray_d[start + i]) };
-                    }
-                    if (have) {
+                        const float4 ro = b.ray_o[start + i], rd = b.ray_d[start + i], ri = b.ray_i[start + i];
+                        node_id = b.P + start + i;
+                        o = xyz(ro), d = xyz(rd), inv = xyz(ri), t_enter = ro.w, t_exit = rd.w;
                         if (STATS) {
                             ++cn.rays;
                             ++cn.rays_by_depth[level];
+                            ++cn.node_tests;
                         }
-                        my = i;
-                        my_mark = tested;
-                        live = w.init<STATS>(S, ws, lane, r, cn);
-                        if (live) {
-                            ws.best[lane] = kNoHitKey;
+                    }
+                    my = i;
+                    my_mark = tested;
+                    live = t_enter <= t_exit;
+                    w.node = -1;
+                    if (live) {
+                        w.start(ws, lane, o, d, inv, t_enter, t_exit);
+                        ws.best[lane] = kNoHitKey;
 #pragma unroll
-                            for (int k = 0; k < kTraceMailbox; ++k)
-                                ws.mailbox[k][lane] = -1;
-                        }
+                        for (int k = 0; k < kTraceMailbox; ++k)
+                            ws.mailbox[k][lane] = -1;
                     }
                 }
             }
@@ -373,6 +347,11 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
         const Candidate cand = load_candidate(S, ws, head, batch, lane);
         head = (head + batch) & (kRing - 1);
         fill -= batch;
+#if CRT_TEST_FIRST
+        test_candidate<STATS>(ws, cand, cn);
+        tested += batch;
+        __syncwarp();
+#endif
         // ---- c. gather the leaves reached last round into the ring
         if (leaves != 0u) {
             int incl = leaf_count;
@@ -427,9 +406,11 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
             leaf_count = 0;
         }
         // ---- d. test the batch loaded in (b)
+#if !CRT_TEST_FIRST
         test_candidate<STATS>(ws, cand, cn);
         tested += batch;
         __syncwarp();
+#endif
         // ---- e. steps of the walk, the first with the node loaded in (a); a leaf is handed over to the next round's
         //         gather and the walk goes on at once (speculatively: its tests have not run yet)
         if (walking) {
@@ -441,10 +422,10 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
                         break;
                     n = __ldg(&S.kd_nodes[w.node]);
                 }
-                if (w.step<STATS>(ws, lane, n, best_t, cn)) {
-                    leaf_first = n.y, leaf_count = n.z;
+                if (w.step<STATS>(ws, lane, n, best_t, cn))
+                    leaf_first = n.y, leaf_count = n.z, w.node = -1;
+                if (w.node < 0) // leaf handed over, or an absent child: one pop site for both
                     w.pop<STATS>(ws, lane, best_t, cn);
-                }
             }
         }
         // ---- f. retire: walk over, nothing left to gather, every candidate tested
@@ -455,7 +436,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
                 h.t = __uint_as_float(unsigned(key >> 32));
                 h.tri = int(unsigned(key & 0xffffffffull));
             }
-            b.hit[level == 0 ? my : b.P + start + my] = make_float2(h.t, __int_as_float(h.tri));
+            b.hit[node_id] = make_float2(h.t, __int_as_float(h.tri));
 #ifdef CRT_DEBUG_TAIL
             atomicMax(&g_tail[level][0], (unsigned long long)rounds);
             atomicAdd(&g_tail[level][1], (unsigned long long)rounds);

@@ -18,14 +18,19 @@ constexpr bool kWavefrontReady = true;
 constexpr int kMaxLevels = kMaxDepthCap + 2;
 
 struct WfCtl {                 // zeroed at the start of every frame
-    int count[kMaxLevels];     // rays per level (level 0 is implicit = P)
+    int count[kMaxLevels];     // rays per level (level 0: primary rays that enter the root box)
     int fetch[kMaxLevels];     // trace kernels' queue cursors
     int pending0;              // non-terminal pixels (entries of `pend`)
     int overflow;              // a level outgrew the pool: the host retries with a larger one
 };
 
 struct WfBuffers {
-    float4 *ray_o, *ray_d; // [cap]      rays of levels >= 1 (w of ray_o: unused)
+    // ray records of levels >= 1, [cap]: {origin, root entry t} {direction, root exit t} {1/direction, -}
+    float4 *ray_o, *ray_d, *ray_i;
+    // primary rays that enter the root box, compacted, [P]: {direction, entry t} {1/direction, exit t} slot
+    // (their origin is the camera position)
+    float4 *ray0_d, *ray0_i;
+    int *ray0_slot;
     float2 *hit;           // [P + cap]  {t, tri as int bits}
     int4 *rec;             // [P + cap]  {kind, first child node id, fresnel bits, 0}
     float4 *alb;           // [P + cap]  reflective albedo
@@ -39,7 +44,8 @@ struct WavefrontState {
     WfBuffers b{};
     size_t node_capacity = 0; // allocated entries of hit
     size_t tree_capacity = 0; // allocated entries of rec/alb/col
-    size_t ray_capacity = 0;  // allocated entries of ray_o/ray_d
+    size_t ray_capacity = 0;  // allocated entries of ray_o/ray_d/ray_i
+    size_t ray0_capacity = 0; // allocated entries of ray0_*
     size_t pend_capacity = 0;
     int sm_count = 0;
     int *h_flags = nullptr;   // pinned: {overflow}
@@ -61,6 +67,61 @@ __device__ __forceinline__ bool slot_pixel(const WfBuffers &b, const DScene &S, 
     x = (patch % b.patches_x) * 8 + (lane & 7);
     ly = (patch / b.patches_x) * 4 + (lane >> 3);
     return x < S.cam.width && ly < P.rows;
+}
+
+// ------------------------------------------------------------------------------------------------ RAYGEN
+// Camera::generate_ray (crt_camera.cpp:7-35) for every pixel slot + entry into the root box, at full SIMD width.
+// Rays that enter the box are appended to the level-0 queue (ballot compaction, one atomicAdd per warp; order stays
+// patch-major so neighbouring queue entries are neighbouring pixels); the others get their miss record right here.
+constexpr int kRaygenBlock = 256;
+
+template <bool STATS>
+__global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
+                                                             const __grid_constant__ WfBuffers b, Counters *__restrict__ counters) {
+    const unsigned lane = threadIdx.x & 31u;
+    Counters cn{};
+    for (int first = blockIdx.x * kRaygenBlock + (threadIdx.x & ~31); first < b.P; first += gridDim.x * kRaygenBlock) {
+        const int slot = first + int(lane);
+        int x, ly;
+        const bool have = slot_pixel(b, S, P, slot, x, ly);
+        Ray r{};
+        RaySetup q{};
+        q.live = false;
+        if (have) {
+            r = generate_ray(S.cam, x, global_row(P, ly));
+            q = ray_setup(S, r);
+            if (STATS) {
+                ++cn.rays;
+                ++cn.rays_by_depth[0];
+                ++cn.node_tests;
+            }
+        }
+        const unsigned live = __ballot_sync(0xffffffffu, q.live);
+        int base = 0;
+        if (live) {
+            if (lane == 0)
+                base = atomicAdd(&b.ctl->count[0], __popc(live));
+            base = __shfl_sync(0xffffffffu, base, 0);
+        }
+        if (q.live) {
+            const int k = base + __popc(live & ((1u << lane) - 1u));
+            b.ray0_d[k] = make_float4(r.d.x, r.d.y, r.d.z, q.tmin);
+            b.ray0_i[k] = make_float4(q.inv.x, q.inv.y, q.inv.z, q.tmax);
+            b.ray0_slot[k] = slot;
+        } else if (have) {
+            b.hit[slot] = make_float2(kInf, __int_as_float(-1));
+        }
+    }
+    if (STATS)
+        flush_counters(cn, counters);
+}
+
+// record of a ray of a level >= 1 (written by the shade stage)
+__device__ __forceinline__ void write_ray(const DScene &S, const WfBuffers &b, int q, V3 o, V3 d) {
+    const RaySetup u = ray_setup(S, Ray{ o, d });
+    b.ray_o[q] = make_float4(o.x, o.y, o.z, u.tmin);
+    b.ray_d[q] = make_float4(d.x, d.y, d.z, u.live ? u.tmax : -1.0f); // exit < entry marks "nothing to walk"
+    b.ray_i[q] = make_float4(u.inv.x, u.inv.y, u.inv.z, 0.0f);
 }
 
 // ------------------------------------------------------------------------------------------------ TRACE
@@ -179,12 +240,9 @@ __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant_
                 ctl->overflow = 1;
                 kind = kTerminal, children = 0, c = zero; // frame is discarded and re-rendered with a larger pool
             } else {
-                b.ray_o[q] = make_float4(o0.x, o0.y, o0.z, 0.0f);
-                b.ray_d[q] = make_float4(d0.x, d0.y, d0.z, 0.0f);
-                if (children == 2) {
-                    b.ray_o[q + 1] = make_float4(o1.x, o1.y, o1.z, 0.0f);
-                    b.ray_d[q + 1] = make_float4(d1.x, d1.y, d1.z, 0.0f);
-                }
+                write_ray(S, b, q, o0, d0);
+                if (children == 2)
+                    write_ray(S, b, q + 1, o1, d1);
                 b.rec[node_id] = make_int4(kind, b.P + q, __float_as_int(fres), 0);
                 b.alb[node_id] = make_float4(albedo.x, albedo.y, albedo.z, 0.0f);
                 if (level == 0)
@@ -239,7 +297,7 @@ __global__ void __launch_bounds__(256) k_wf_resolve(const __grid_constant__ DSce
 
 // ------------------------------------------------------------------------------------------------ host driver
 inline void wavefront_free(WavefrontState &w) {
-    cudaFree(w.b.ray_o), cudaFree(w.b.ray_d), cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col), cudaFree(w.b.pend),
+    cudaFree(w.b.ray_o), cudaFree(w.b.ray_d), cudaFree(w.b.ray_i), cudaFree(w.b.ray0_d), cudaFree(w.b.ray0_i), cudaFree(w.b.ray0_slot), cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col), cudaFree(w.b.pend),
         cudaFree(w.b.ctl);
     cudaFreeHost(w.h_flags);
     w = WavefrontState{};
@@ -280,13 +338,26 @@ inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
         w.tree_capacity = nodes;
     }
     if (cap > w.ray_capacity) {
-        cudaFree(w.b.ray_o), cudaFree(w.b.ray_d);
-        w.b.ray_o = nullptr, w.b.ray_d = nullptr, w.ray_capacity = 0;
+        cudaFree(w.b.ray_o), cudaFree(w.b.ray_d), cudaFree(w.b.ray_i);
+        w.b.ray_o = nullptr, w.b.ray_d = nullptr, w.b.ray_i = nullptr, w.ray_capacity = 0;
+        if ((e = cudaMalloc(&w.b.ray_i, cap * sizeof(float4))) != cudaSuccess)
+            return e;
         if ((e = cudaMalloc(&w.b.ray_o, cap * sizeof(float4))) != cudaSuccess)
             return e;
         if ((e = cudaMalloc(&w.b.ray_d, cap * sizeof(float4))) != cudaSuccess)
             return e;
         w.ray_capacity = cap;
+    }
+    if (size_t(P) > w.ray0_capacity) {
+        cudaFree(w.b.ray0_d), cudaFree(w.b.ray0_i), cudaFree(w.b.ray0_slot);
+        w.b.ray0_d = nullptr, w.b.ray0_i = nullptr, w.b.ray0_slot = nullptr, w.ray0_capacity = 0;
+        if ((e = cudaMalloc(&w.b.ray0_d, size_t(P) * sizeof(float4))) != cudaSuccess)
+            return e;
+        if ((e = cudaMalloc(&w.b.ray0_i, size_t(P) * sizeof(float4))) != cudaSuccess)
+            return e;
+        if ((e = cudaMalloc(&w.b.ray0_slot, size_t(P) * sizeof(int))) != cudaSuccess)
+            return e;
+        w.ray0_capacity = size_t(P);
     }
     if (secondary && size_t(P) > w.pend_capacity) {
         cudaFree(w.b.pend);
@@ -324,6 +395,14 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     const int levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
     const int trace_blocks = w.sm_count * 8;
     int n = 0;
+    if (traversal != CRT_TRAVERSAL_LITERAL) {
+        const int rb = min(w.sm_count * 16, (P + kRaygenBlock - 1) / kRaygenBlock);
+        if (stats)
+            k_wf_raygen<true><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters);
+        else
+            k_wf_raygen<false><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters);
+        ++n;
+    }
     for (int level = 0; level < levels; ++level) {
         const int tb = level == 0 ? min(trace_blocks, (P + kTraceBlock - 1) / kTraceBlock) : trace_blocks;
         if (traversal == CRT_TRAVERSAL_LITERAL)
