@@ -45,9 +45,10 @@ class FlatScene(C.Structure):
         ("root_min", C.c_float * 3), ("root_max", C.c_float * 3),
         ("n_triangles", C.c_int32), ("n_vertices", C.c_int32), ("n_nodes", C.c_int32), ("n_refs", C.c_int32),
         ("n_lights", C.c_int32), ("n_materials", C.c_int32), ("n_textures", C.c_int32), ("n_texels", C.c_int32),
-        ("max_depth", C.c_int32), ("pad", C.c_int32),
+        ("max_depth", C.c_int32), ("fast_max_depth", C.c_int32), ("n_fast_nodes", C.c_int32), ("n_fast_refs", C.c_int32),
         ("tri_verts", C.c_void_p), ("tri_meta", C.c_void_p), ("vert_normal", C.c_void_p), ("vert_uv", C.c_void_p),
-        ("box_nodes", C.c_void_p), ("kd_nodes", C.c_void_p), ("refs", C.c_void_p), ("lights", C.c_void_p),
+        ("box_nodes", C.c_void_p), ("kd_nodes", C.c_void_p), ("refs", C.c_void_p),
+        ("fast_nodes", C.c_void_p), ("fast_refs", C.c_void_p), ("lights", C.c_void_p),
         ("materials", C.c_void_p), ("textures", C.c_void_p), ("texels", C.c_void_p),
     ]
 
@@ -68,6 +69,8 @@ class FlatScene(C.Structure):
             "box_nodes": self._view(self.box_nodes, self.n_nodes * 8, np.int32).reshape(-1, 8),
             "kd_nodes": self._view(self.kd_nodes, self.n_nodes * 4, np.int32).reshape(-1, 4),
             "refs": self._view(self.refs, self.n_refs, np.uint32),
+            "fast_nodes": self._view(self.fast_nodes, self.n_fast_nodes * 4, np.int32).reshape(-1, 4),
+            "fast_refs": self._view(self.fast_refs, self.n_fast_refs, np.uint32),
             "lights": self._view(self.lights, self.n_lights * 4, np.float32).reshape(-1, 4),
             "materials": self._view(self.materials, self.n_materials * 4, np.int32).reshape(-1, 4),
             "textures": self._view(self.textures, self.n_textures * 12, np.int32).reshape(-1, 12),

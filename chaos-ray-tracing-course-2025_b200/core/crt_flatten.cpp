@@ -1,7 +1,10 @@
 #include "crt_flatten.h"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <unordered_map>
 
 namespace crt {
 
@@ -17,6 +20,180 @@ crt_camera flatten_camera(const Camera &camera) {
     c.width = camera.resolution_x();
     c.height = camera.resolution_y();
     return c;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// The tree the k-d walk traverses.
+//
+// The reference builder (src/core/crt_acceleration_tree.cpp:31-85) splits at the spatial median of axis depth % 3
+// until a node holds <= 16 triangles, whatever the split achieves.  Where triangles are larger than the cells (every
+// bundled mesh; the 1 M-triangle height field ends with cells of 0.04 x 0.003 x 0.04 around triangles of 0.03) most
+// splits separate nothing: both children keep nearly all of the parent's triangles, 56 % of the height field's leaves
+// hold a list identical to another leaf's, and a ray walks ten nodes per leaf to re-find triangles it has tested.
+// The closest hit does not depend on how space is cut (the walk keeps min (t, parse index) over everything it tests),
+// so the flattener is free to UNDO splits that do not pay:
+//   * bottom-up, a subtree is replaced by one leaf holding the union of its triangles when the expected cost of the
+//     leaf (fixed + per-triangle) is not above the expected cost of walking the subtree (node + children weighted by
+//     the surface-area ratio of their boxes: the standard SAH estimate, evaluated on the reference's own boxes);
+//   * identical leaf lists are stored once.
+// Topology, split planes and boxes of the surviving nodes are the reference's; CRT_TREE_COLLAPSE=0 keeps every node.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+float env_float(const char *name, float fallback) {
+    const char *v = std::getenv(name);
+    return v && *v ? float(std::atof(v)) : fallback;
+}
+
+float half_area(const AABB &b) {
+    const float dx = b.max.x - b.min.x, dy = b.max.y - b.min.y, dz = b.max.z - b.min.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+struct ListKey {
+    const uint32_t *data;
+    uint32_t count;
+    bool operator==(const ListKey &o) const { return count == o.count && std::memcmp(data, o.data, size_t(count) * 4) == 0; }
+};
+struct ListHash {
+    size_t operator()(const ListKey &k) const {
+        uint64_t h = 1469598103934665603ull ^ k.count;
+        for (uint32_t i = 0; i < k.count; ++i)
+            h = (h ^ k.data[i]) * 1099511628211ull;
+        return size_t(h);
+    }
+};
+
+} // namespace
+
+FastTreeStats build_fast_tree(const AccelerationTree &tree, const std::vector<Triangle> &triangles, FlatScene &out) {
+    FastTreeStats stats;
+    out.fast_nodes.clear();
+    out.fast_refs.clear();
+    const size_t n = tree.size();
+    if (n == 0)
+        return stats;
+    const bool collapse = env_float("CRT_TREE_COLLAPSE", 1.0f) != 0.0f;
+    // costs in units of one node step of the trace kernel (instruction counts of the stages)
+    const float c_node = env_float("CRT_SAH_NODE", 1.0f), c_leaf = env_float("CRT_SAH_LEAF", 2.0f), c_tri = env_float("CRT_SAH_TRI", 2.8f);
+    const uint32_t max_list = uint32_t(env_float("CRT_SAH_MAX_LEAF", 64.0f));
+
+    // per node: expected cost of its subtree as decided so far, and (when small) the sorted union of its triangles
+    std::vector<float> cost(n, 0.0f);
+    std::vector<uint8_t> is_leaf(n, 0);
+    std::vector<uint32_t> arena;           // unions, appended as they are formed
+    std::vector<uint64_t> span(n, 0);      // offset << 8 | count ; count 255 = "too large, not kept"
+    arena.reserve(tree.references.size() * 2);
+    auto set_span = [&](size_t i, size_t offset, size_t count) { span[i] = (uint64_t(offset) << 8) | uint64_t(count); };
+    auto span_count = [&](size_t i) { return uint32_t(span[i] & 0xff); };
+    auto span_data = [&](size_t i) { return arena.data() + (span[i] >> 8); };
+    std::vector<uint32_t> merged;
+    for (size_t k = n; k-- > 0;) { // children have larger indices than their parent (DFS pre-order)
+        const AccelerationTreeNode &node = tree[k];
+        if (node.is_leaf()) {
+            const size_t offset = arena.size();
+            arena.insert(arena.end(), tree.references.begin() + node.first_reference, tree.references.begin() + node.first_reference + node.reference_count);
+            std::sort(arena.begin() + offset, arena.end());
+            const size_t count = size_t(node.reference_count);
+            is_leaf[k] = 1;
+            cost[k] = c_leaf + c_tri * float(count);
+            if (count < 255)
+                set_span(k, offset, count);
+            else { // cannot take part in a merge; emitted from the reference's own list
+                arena.resize(offset);
+                set_span(k, 0, 255);
+            }
+            continue;
+        }
+        const int c0 = node.children_indices[0], c1 = node.children_indices[1];
+        const float area = half_area(node.bounds);
+        float inner = c_node;
+        bool small = true;
+        merged.clear();
+        for (int c : { c0, c1 }) {
+            if (c < 0)
+                continue;
+            const float p = area > 0.0f ? std::min(1.0f, half_area(tree[size_t(c)].bounds) / area) : 1.0f;
+            inner += p * cost[size_t(c)];
+            if (span_count(size_t(c)) == 255)
+                small = false;
+        }
+        if (small) {
+            if (c0 >= 0 && c1 >= 0) {
+                merged.resize(span_count(size_t(c0)) + span_count(size_t(c1)));
+                merged.resize(size_t(std::set_union(span_data(size_t(c0)), span_data(size_t(c0)) + span_count(size_t(c0)), span_data(size_t(c1)),
+                                                    span_data(size_t(c1)) + span_count(size_t(c1)), merged.begin()) -
+                                     merged.begin()));
+            } else if (c0 >= 0 || c1 >= 0) {
+                const size_t c = size_t(c0 >= 0 ? c0 : c1);
+                merged.assign(span_data(c), span_data(c) + span_count(c));
+            }
+            small = merged.size() <= max_list && merged.size() < 255;
+        }
+        cost[k] = inner;
+        set_span(k, 0, 255);
+        if (small) {
+            const size_t offset = arena.size();
+            arena.insert(arena.end(), merged.begin(), merged.end());
+            set_span(k, offset, merged.size());
+            const float as_leaf = c_leaf + c_tri * float(merged.size());
+            if (collapse && !merged.empty() && as_leaf <= inner) {
+                is_leaf[k] = 1;
+                cost[k] = as_leaf;
+            }
+        }
+    }
+
+    // emit: DFS pre-order from the root, child0's subtree first (the reference's order), leaf lists deduplicated
+    std::unordered_map<ListKey, uint32_t, ListHash> seen;
+    std::vector<uint32_t> list;
+    struct Item {
+        int node, parent_slot, which, depth;
+    };
+    std::vector<Item> todo{ { 0, -1, 0, 0 } };
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        const size_t k = size_t(it.node);
+        const AccelerationTreeNode &node = tree[k];
+        const int self = int(out.fast_nodes.size());
+        if (it.parent_slot >= 0)
+            (it.which == 0 ? out.fast_nodes[size_t(it.parent_slot)].a : out.fast_nodes[size_t(it.parent_slot)].b) = self;
+        stats.max_depth = std::max(stats.max_depth, it.depth);
+        if (is_leaf[k]) {
+            const uint32_t *data;
+            uint32_t count;
+            if (span_count(k) == 255) {
+                data = tree.references.data() + node.first_reference, count = uint32_t(node.reference_count);
+            } else {
+                data = span_data(k), count = span_count(k);
+            }
+            auto found = seen.find(ListKey{ data, count });
+            uint32_t first;
+            if (found != seen.end()) {
+                first = found->second;
+            } else {
+                first = uint32_t(out.fast_refs.size());
+                for (uint32_t i = 0; i < count; ++i)
+                    out.fast_refs.push_back(data[i] | (triangles[data[i]].flags.back_face_culling ? CRT_REF_CULL_BIT : 0u));
+                seen.emplace(ListKey{ data, count }, first); // key points into arena / tree.references: both stay put
+            }
+            out.fast_nodes.push_back({ 0.0f, int32_t(first), int32_t(count), 3 });
+            ++stats.leaves;
+            stats.max_leaf = std::max(stats.max_leaf, int(count));
+        } else {
+            const int axis = node.depth % 3;
+            out.fast_nodes.push_back({ (node.bounds.min.data[axis] + node.bounds.max.data[axis]) * 0.5f, -1, -1, axis });
+            // pushed in reverse so that child0 is emitted first
+            if (node.children_indices[1] >= 0)
+                todo.push_back({ node.children_indices[1], self, 1, it.depth + 1 });
+            if (node.children_indices[0] >= 0)
+                todo.push_back({ node.children_indices[0], self, 0, it.depth + 1 });
+        }
+    }
+    stats.nodes = int(out.fast_nodes.size());
+    stats.refs = int(out.fast_refs.size());
+    return stats;
 }
 
 void flatten_scene(const Scene &scene, FlatScene &out) {
@@ -114,6 +291,12 @@ void flatten_scene(const Scene &scene, FlatScene &out) {
     v.n_textures = int32_t(out.textures.size());
     v.n_texels = int32_t(out.texels.size());
     v.max_depth = tree.max_depth;
+    const FastTreeStats fast = build_fast_tree(tree, scene.triangles, out);
+    v.fast_max_depth = fast.max_depth;
+    v.n_fast_nodes = fast.nodes;
+    v.n_fast_refs = fast.refs;
+    v.fast_nodes = out.fast_nodes.data();
+    v.fast_refs = out.fast_refs.data();
     v.tri_verts = out.tri_verts.data();
     v.tri_meta = out.tri_meta.data();
     v.vert_normal = out.vert_normal.data();

@@ -17,6 +17,8 @@ struct FlatScene {
     std::vector<crt_box_node> box_nodes;
     std::vector<crt_kd_node> kd_nodes;
     std::vector<uint32_t> refs;
+    std::vector<crt_kd_node> fast_nodes; // the tree the k-d walk uses: same topology, subtrees merged by cost
+    std::vector<uint32_t> fast_refs;     // its leaf lists, identical lists stored once
     std::vector<crt_float4> lights;
     std::vector<crt_material> materials;
     std::vector<crt_texture> textures;
@@ -26,5 +28,11 @@ struct FlatScene {
 
 crt_camera flatten_camera(const Camera &camera);
 void flatten_scene(const Scene &scene, FlatScene &out);
+
+// Derives the walk tree from the reference tree (crt_flatten.cpp); exposed for tests.
+struct FastTreeStats {
+    int nodes{ 0 }, leaves{ 0 }, refs{ 0 }, max_depth{ 0 }, max_leaf{ 0 };
+};
+FastTreeStats build_fast_tree(const AccelerationTree &tree, const std::vector<Triangle> &triangles, FlatScene &out);
 
 } // namespace crt

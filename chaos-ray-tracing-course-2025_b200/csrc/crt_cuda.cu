@@ -280,7 +280,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         return fail(ctx, CRT_ERR_INVALID, "scene is NULL");
     if (s->n_nodes < 1 || !s->box_nodes || !s->kd_nodes)
         return fail(ctx, CRT_ERR_INVALID, "scene has no acceleration tree");
-    if (s->max_depth + 2 > kStack)
+    if (s->n_fast_nodes < 1 || !s->fast_nodes)
+        return fail(ctx, CRT_ERR_INVALID, "scene has no walk tree (fast_nodes)");
+    if (s->max_depth + 2 > kStack || s->fast_max_depth + 2 > kStack)
         return fail(ctx, CRT_ERR_INVALID, "acceleration tree deeper than the traversal stack");
     if (s->camera.width < 0 || s->camera.height < 0)
         return fail(ctx, CRT_ERR_INVALID, "negative image size");
@@ -291,18 +293,19 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         size_t bytes;
         size_t offset;
     };
-    Part parts[11] = {
+    Part parts[12] = {
         { s->tri_verts, size_t(s->n_triangles) * 3 * sizeof(crt_float4), 0 },
         { s->tri_meta, size_t(s->n_triangles) * 4 * sizeof(int32_t), 0 },
         { s->vert_normal, size_t(s->n_vertices) * sizeof(crt_float4), 0 },
         { s->vert_uv, size_t(s->n_vertices) * 2 * sizeof(float), 0 },
         { s->box_nodes, size_t(s->n_nodes) * sizeof(crt_box_node), 0 },
-        { s->kd_nodes, size_t(s->n_nodes) * sizeof(crt_kd_node), 0 },
+        { s->fast_nodes, size_t(s->n_fast_nodes) * sizeof(crt_kd_node), 0 },
         { s->refs, size_t(s->n_refs) * sizeof(uint32_t), 0 },
         { s->lights, size_t(s->n_lights) * sizeof(crt_float4), 0 },
         { s->materials, size_t(s->n_materials) * sizeof(crt_material), 0 },
         { s->textures, size_t(s->n_textures) * sizeof(crt_texture), 0 },
         { s->texels, size_t(s->n_texels) * sizeof(crt_float4), 0 },
+        { s->fast_refs, size_t(s->n_fast_refs) * sizeof(uint32_t), 0 },
     };
     size_t total = 0;
     for (Part &p : parts) {
@@ -349,6 +352,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     d.materials = reinterpret_cast<const int4 *>(ctx->d_arena + parts[8].offset);
     d.textures = reinterpret_cast<const float4 *>(ctx->d_arena + parts[9].offset);
     d.texels = reinterpret_cast<const float4 *>(ctx->d_arena + parts[10].offset);
+    d.kd_refs = reinterpret_cast<const uint32_t *>(ctx->d_arena + parts[11].offset);
     ctx->has_secondary = false;
     for (int i = 0; i < s->n_materials; ++i)
         if ((s->materials[i].type == 1 && s->reflections_on) || (s->materials[i].type == 2 && s->refractions_on))

@@ -27,8 +27,9 @@ struct DScene {
     const float4 *__restrict__ vert_normal; // 1 per vertex
     const float2 *__restrict__ vert_uv;     // 1 per vertex
     const float4 *__restrict__ box_nodes;   // 2 per node
-    const int4 *__restrict__ kd_nodes;      // 1 per node
-    const uint32_t *__restrict__ refs;
+    const int4 *__restrict__ kd_nodes;      // 1 per node of the walk tree (crt_flat_scene.fast_nodes)
+    const uint32_t *__restrict__ kd_refs;   // its leaf lists (crt_flat_scene.fast_refs)
+    const uint32_t *__restrict__ refs;      // leaf lists of the reference tree (box_nodes)
     const float4 *__restrict__ lights;
     const int4 *__restrict__ materials;
     const float4 *__restrict__ textures; // 3 float4 per texture (crt_texture is 48 B)
@@ -454,7 +455,7 @@ struct KdWalker {
         if (leaf.w < 0)
             return;
         for (int i = 0; i < leaf.z; ++i)
-            test_ref<STATS>(S, __ldg(&S.refs[leaf.y + i]), cn, mailbox, mailbox_stride);
+            test_ref<STATS>(S, __ldg(&S.kd_refs[leaf.y + i]), cn, mailbox, mailbox_stride);
         pop<STATS>(cn);
     }
 };

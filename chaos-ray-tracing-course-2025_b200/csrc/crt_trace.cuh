@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
                 bool keep = false;
                 uint32_t ref = 0;
                 if (item < items) {
-                    ref = __ldg(&S.refs[owner_first + (item - owner_excl)]);
+                    ref = __ldg(&S.kd_refs[owner_first + (item - owner_excl)]);
                     const int tri = int(ref & 0x7FFFFFFFu);
                     int *slot = &ws.mailbox[(uint32_t(tri) * 0x9E3779B1u) >> (32 - kMailboxBits)][owner];
                     keep = *slot != tri;

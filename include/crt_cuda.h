@@ -50,9 +50,12 @@ typedef struct crt_box_node {
     int32_t right;
 } crt_box_node;
 
-/* 16 B node of the fast traversal.  Because every child box is its parent's box cut at the midpoint of
+/* 16 B node of the k-d walk.  Because every child box is its parent's box cut at the midpoint of
  * axis depth%3 (crt_aabb.h:24-35), the tree is a k-d tree: an inner node is fully described by the cut.
- * inner: {split plane, child0 (or -1), child1 (or -1), axis 0..2};  leaf: {0, first_ref, count, 3}. */
+ * inner: {split plane, child0 (or -1), child1 (or -1), axis 0..2};  leaf: {0, first_ref, count, 3}.
+ * Two arrays use it: kd_nodes mirrors the reference tree node for node (same indices as box_nodes, leaf lists in
+ * refs); fast_nodes is what CRT_TRAVERSAL_KD walks: the same tree after the flattener merged the subtrees whose
+ * splits do not pay (cost estimate on the reference's boxes) and stored identical leaf lists once (fast_refs). */
 typedef struct crt_kd_node {
     float split;
     int32_t a;
@@ -100,7 +103,8 @@ typedef struct crt_flat_scene {
     float root_min[3], root_max[3];
     int32_t n_triangles, n_vertices, n_nodes, n_refs, n_lights, n_materials, n_textures, n_texels;
     int32_t max_depth; /* depth of the deepest node (root = 0) */
-    int32_t pad;
+    int32_t fast_max_depth;
+    int32_t n_fast_nodes, n_fast_refs;
     const crt_float4 *tri_verts;   /* 3 per triangle: {v0.xyz, N.x} {v1.xyz, N.y} {v2.xyz, N.z}; parse order */
     const int32_t *tri_meta;       /* 4 per triangle: vertex indices i0,i1,i2, material | flag bits         */
     const crt_float4 *vert_normal; /* 1 per vertex: smooth normal xyz (crt_mesh.cpp:19-29)                  */
@@ -108,6 +112,8 @@ typedef struct crt_flat_scene {
     const crt_box_node *box_nodes; /* n_nodes, DFS pre-order exactly as the reference builds them           */
     const crt_kd_node *kd_nodes;   /* n_nodes, same indexing                                                */
     const uint32_t *refs;          /* n_refs leaf references, leaf order = parse order within a leaf        */
+    const crt_kd_node *fast_nodes; /* n_fast_nodes, DFS pre-order                                           */
+    const uint32_t *fast_refs;     /* n_fast_refs, ascending triangle index within a leaf                   */
     const crt_float4 *lights;      /* {position.xyz, intensity}, file order                                 */
     const crt_material *materials;
     const crt_texture *textures;

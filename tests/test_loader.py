@@ -159,3 +159,44 @@ def test_tree_rules_on_a_synthetic_grid(crt):
     for i in np.nonzero(leaf)[0][:50]:
         for t in refs[-left[i] - 2: -left[i] - 2 + right[i]]:
             assert (tv[t].min(0) <= maxs[i]).all() and (tv[t].max(0) >= mins[i]).all()
+
+
+@pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "15-01-conclusion/scene2.crtscene", "11-01-refractive/scene3.crtscene"])
+def test_walk_tree_is_the_reference_tree_with_subtrees_merged(crt, ot, rel):
+    """fast_nodes / fast_refs (what CRT_TRAVERSAL_KD walks): same split planes and topology as the reference tree,
+    every merged leaf holds exactly the triangles of the reference subtree it replaces."""
+    scene = crt.Scene.load_file(ot.scene_file(rel))
+    flat = scene.flatten()
+    a = flat.arrays()
+    kd, refs, fast, frefs = a["kd_nodes"], a["refs"] & 0x7FFFFFFF, a["fast_nodes"], a["fast_refs"]
+    assert flat.n_fast_nodes == len(fast) <= flat.n_nodes and flat.fast_max_depth <= flat.max_depth
+
+    def subtree_triangles(i):
+        if kd[i, 3] == 3:
+            return set(refs[kd[i, 1]:kd[i, 1] + kd[i, 2]].tolist())
+        out = set()
+        for c in (kd[i, 1], kd[i, 2]):
+            if c >= 0:
+                out |= subtree_triangles(c)
+        return out
+
+    # walk both trees in lock step from the roots
+    todo, seen_fast = [(0, 0)], 0
+    while todo:
+        i, j = todo.pop()
+        seen_fast += 1
+        if fast[j, 3] == 3:
+            lst = (frefs[fast[j, 1]:fast[j, 1] + fast[j, 2]] & 0x7FFFFFFF).tolist()
+            assert lst == sorted(set(lst)), "leaf lists are ascending and duplicate-free"
+            assert set(lst) == subtree_triangles(i)
+            cull = frefs[fast[j, 1]:fast[j, 1] + fast[j, 2]] >> 31
+            assert np.array_equal(cull, (a["tri_meta"][lst, 3] >> 25) & 1)
+        else:
+            assert kd[i, 3] == fast[j, 3] and kd[i, 0] == fast[j, 0], "same axis and split plane"
+            for col in (1, 2):
+                assert (kd[i, col] >= 0) == (fast[j, col] >= 0)
+                if kd[i, col] >= 0:
+                    todo.append((kd[i, col], fast[j, col]))
+            if fast[j, 1] >= 0:
+                assert fast[j, 1] == j + 1, "child0 follows its parent (DFS pre-order)"
+    assert seen_fast == len(fast)
