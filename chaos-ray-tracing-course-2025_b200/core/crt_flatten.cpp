@@ -1,4 +1,5 @@
 #include "crt_flatten.h"
+#include "crt_kdbuild.h"
 
 #include <algorithm>
 #include <cmath>
@@ -291,10 +292,24 @@ void flatten_scene(const Scene &scene, FlatScene &out) {
     v.n_textures = int32_t(out.textures.size());
     v.n_texels = int32_t(out.texels.size());
     v.max_depth = tree.max_depth;
-    const FastTreeStats fast = build_fast_tree(tree, scene.triangles, out);
-    v.fast_max_depth = fast.max_depth;
-    v.n_fast_nodes = fast.nodes;
-    v.n_fast_refs = fast.refs;
+    // the walk tree: an SAH k-d tree of our own (crt_kdbuild.cpp) unless CRT_WALK_TREE=reference asks for the
+    // reference's tree with the non-paying splits merged (build_fast_tree above)
+    const char *which = std::getenv("CRT_WALK_TREE");
+    if (which && std::strcmp(which, "reference") == 0) {
+        const FastTreeStats fast = build_fast_tree(tree, scene.triangles, out);
+        v.fast_max_depth = fast.max_depth;
+        v.n_fast_nodes = fast.nodes;
+        v.n_fast_refs = fast.refs;
+    } else {
+        std::vector<uint8_t> cull(n_tri);
+        for (size_t i = 0; i < n_tri; ++i)
+            cull[i] = scene.triangles[i].flags.back_face_culling ? 1 : 0;
+        const KdBuildStats fast = build_sah_tree(out.tri_verts.data(), n_tri, cull.data(), v.root_min, v.root_max, KdBuildParams::from_environment(),
+                                                 out.fast_nodes, out.fast_refs);
+        v.fast_max_depth = fast.max_depth;
+        v.n_fast_nodes = fast.nodes;
+        v.n_fast_refs = fast.refs;
+    }
     v.fast_nodes = out.fast_nodes.data();
     v.fast_refs = out.fast_refs.data();
     v.tri_verts = out.tri_verts.data();

@@ -162,9 +162,10 @@ def test_tree_rules_on_a_synthetic_grid(crt):
 
 
 @pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "15-01-conclusion/scene2.crtscene", "11-01-refractive/scene3.crtscene"])
-def test_walk_tree_is_the_reference_tree_with_subtrees_merged(crt, ot, rel):
-    """fast_nodes / fast_refs (what CRT_TRAVERSAL_KD walks): same split planes and topology as the reference tree,
+def test_walk_tree_is_the_reference_tree_with_subtrees_merged(crt, ot, rel, monkeypatch):
+    """CRT_WALK_TREE=reference: fast_nodes / fast_refs have the split planes and topology of the reference tree,
     every merged leaf holds exactly the triangles of the reference subtree it replaces."""
+    monkeypatch.setenv("CRT_WALK_TREE", "reference")
     scene = crt.Scene.load_file(ot.scene_file(rel))
     flat = scene.flatten()
     a = flat.arrays()
@@ -200,3 +201,50 @@ def test_walk_tree_is_the_reference_tree_with_subtrees_merged(crt, ot, rel):
             if fast[j, 1] >= 0:
                 assert fast[j, 1] == j + 1, "child0 follows its parent (DFS pre-order)"
     assert seen_fast == len(fast)
+
+
+@needs_scenes
+@pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "15-01-conclusion/scene2.crtscene", "11-01-refractive/scene3.crtscene",
+                                 "12-01-textures/scene4.crtscene", "14-01-acceleration-tree/scene0.crtscene"])
+def test_sah_walk_tree_invariants(crt, ot, rel):
+    """The default walk tree (core/crt_kdbuild.cpp): a k-d tree over the root box whose leaves list every triangle
+    that reaches into their cell -- the property the closest-hit walk needs, whatever the split planes are."""
+    scene = crt.Scene.load_file(ot.scene_file(rel))
+    flat = scene.flatten()
+    a = flat.arrays()
+    fast, frefs = a["fast_nodes"], a["fast_refs"]
+    tv = a["tri_verts"][:, :, :3]
+    lo, hi = tv.min(1), tv.max(1)
+    assert flat.n_fast_nodes == len(fast) and flat.n_fast_refs == len(frefs) and flat.fast_max_depth + 2 <= 48
+    root_lo, root_hi = np.array(list(flat.root_min), dtype=np.float32), np.array(list(flat.root_max), dtype=np.float32)
+    seen_nodes, listed, max_depth = 0, set(), 0
+    todo = [(0, root_lo, root_hi, np.arange(flat.n_triangles), 0)]
+    while todo:
+        j, clo, chi, members, depth = todo.pop()
+        seen_nodes += 1
+        max_depth = max(max_depth, depth)
+        split, c0, c1, axis = fast[j, 0].view(np.float32), int(fast[j, 1]), int(fast[j, 2]), int(fast[j, 3])
+        if axis == 3:
+            lst = frefs[c0:c0 + c1]
+            ids = (lst & 0x7FFFFFFF).astype(np.int64)
+            assert c1 > 0 and np.array_equal(ids, members), "leaf list = the triangles routed here, ascending"
+            assert np.array_equal(lst >> 31, (a["tri_meta"][ids, 3] >> 25) & 1)
+            # geometric reading of the same rule: whatever overlaps the cell's interior is listed
+            inside = np.nonzero(((lo < chi) & (hi > clo)).all(1))[0]
+            assert set(inside.tolist()) <= set(ids.tolist())
+            listed |= set(ids.tolist())
+            continue
+        assert axis in (0, 1, 2) and clo[axis] < split < chi[axis] or flat.n_triangles == 0
+        flat_in_plane = (lo[members, axis] == split) & (hi[members, axis] == split)
+        left = members[(lo[members, axis] < split) | flat_in_plane]
+        right = members[(hi[members, axis] > split) | flat_in_plane]
+        assert (c0 >= 0) == (len(left) > 0) and (c1 >= 0) == (len(right) > 0), "absent child <=> nothing on that side"
+        if c0 >= 0:
+            assert c0 == j + 1, "child0 follows its parent (DFS pre-order)"
+            h = chi.copy(); h[axis] = split
+            todo.append((c0, clo, h, left, depth + 1))
+        if c1 >= 0:
+            l = clo.copy(); l[axis] = split
+            todo.append((c1, l, chi, right, depth + 1))
+    assert seen_nodes == len(fast) and max_depth == flat.fast_max_depth
+    assert listed == set(range(flat.n_triangles)), "every triangle is reachable"
