@@ -2,6 +2,7 @@
 // There is no CPU fallback anywhere in this file: without a CUDA device every entry point fails loudly.
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -23,6 +24,7 @@ struct crt_cuda_ctx {
     DScene scene{};
     bool have_scene = false;
     bool has_secondary = false; // some material can spawn reflection / refraction rays
+    bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
     crt_render_params last_params{};
     bool last_wavefront = false;
 
@@ -165,7 +167,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         if (pipeline == CRT_PIPELINE_WAVEFRONT) {
             int launches = 0;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
-                                             ctx->d_counters, ctx->stream, &launches);
+                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves);
             ctx->last_wavefront = true;
             if (e != cudaSuccess)
                 return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
@@ -357,6 +359,13 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     for (int i = 0; i < s->n_materials; ++i)
         if ((s->materials[i].type == 1 && s->reflections_on) || (s->materials[i].type == 2 && s->refractions_on))
             ctx->has_secondary = true;
+    // which trace kernel suits the walk tree: mean triangles per leaf (CRT_TRACE_KERNEL=heavy|light overrides)
+    size_t leaves = 0;
+    for (int i = 0; i < s->n_fast_nodes; ++i)
+        leaves += s->fast_nodes[i].axis == 3;
+    ctx->light_leaves = leaves > 0 && double(s->n_fast_refs) / double(leaves) <= 6.0;
+    if (const char *k = std::getenv("CRT_TRACE_KERNEL"); k && *k)
+        ctx->light_leaves = std::strcmp(k, "light") == 0;
     ctx->have_scene = true;
     return CRT_OK;
 }

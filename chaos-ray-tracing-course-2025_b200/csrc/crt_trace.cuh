@@ -76,7 +76,8 @@ struct TraceWalker {
     uint2 spill[kStack];
 
     // start a walk from a ray record (entry/exit of the root box and 1/direction come with the record)
-    __device__ __forceinline__ void start(TraceWarpShared &ws, unsigned lane, V3 o, V3 d, V3 inv, float t_enter, float t_exit) {
+    template <class WS>
+    __device__ __forceinline__ void start(WS &ws, unsigned lane, V3 o, V3 d, V3 inv, float t_enter, float t_exit) {
         sp = 0, lo = 0, flagged = 0;
         tmin = t_enter, tmax = t_exit, root_tmax = t_exit;
         node = 0;
@@ -88,7 +89,8 @@ struct TraceWalker {
     __device__ __forceinline__ bool done() const { return node < 0; }
 
     // the store happens whether or not anything is pushed (slot sp is free), only the count moves: no branch per push
-    __device__ __forceinline__ void push_if(TraceWarpShared &ws, unsigned lane, bool doit, uint32_t tagged_node, float entry) {
+    template <class WS>
+    __device__ __forceinline__ void push_if(WS &ws, unsigned lane, bool doit, uint32_t tagged_node, float entry) {
         const bool full = sp - lo == kWin;
         if (doit & full) { // window full (rare): the oldest entry goes to local memory
             spill[lo] = ws.stack[lo & (kWin - 1)][lane];
@@ -99,13 +101,14 @@ struct TraceWalker {
         sp += doit ? 1 : 0;
     }
 
-    __device__ __forceinline__ uint2 entry_at(const TraceWarpShared &ws, unsigned lane, int i) const {
+    template <class WS>
+    __device__ __forceinline__ uint2 entry_at(const WS &ws, unsigned lane, int i) const {
         return i >= lo ? ws.stack[i & (kWin - 1)][lane] : spill[i];
     }
 
     // next pending subtree that can still hold a closer (or equal) hit; node = -1 when none is left
-    template <bool STATS>
-    __device__ __forceinline__ void pop(TraceWarpShared &ws, unsigned lane, float best_t, Counters &cn) {
+    template <bool STATS, class WS>
+    __device__ __forceinline__ void pop(WS &ws, unsigned lane, float best_t, Counters &cn) {
         for (;;) {
             if (sp == 0) {
                 node = -1;
@@ -146,8 +149,8 @@ struct TraceWalker {
     // ONE node of the walk: true when `n` is a leaf.  Same decisions as KdWalker::step, written as selects so that
     // the lanes of a warp, which sit at unrelated nodes, share one instruction stream; only the push and the pop stay
     // conditional.
-    template <bool STATS>
-    __device__ __forceinline__ bool step(TraceWarpShared &ws, unsigned lane, const int4 n, float best_t, Counters &cn) {
+    template <bool STATS, class WS>
+    __device__ __forceinline__ bool step(WS &ws, unsigned lane, const int4 n, float best_t, Counters &cn) {
         if (n.w == 3)
             return true;
         const int axis = n.w;

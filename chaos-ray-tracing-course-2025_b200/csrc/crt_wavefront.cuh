@@ -127,6 +127,7 @@ __device__ __forceinline__ void write_ray(const DScene &S, const WfBuffers &b, i
 // ------------------------------------------------------------------------------------------------ TRACE
 } // namespace crtdev
 #include "crt_trace.cuh"
+#include "crt_trace_light.cuh"
 namespace crtdev {
 
 // ------------------------------------------------------------------------------------------------ SHADE
@@ -373,7 +374,14 @@ inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
 
 template <int TRAV>
 inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, const DParams &dp, bool stats, int level, int blocks, Counters *counters,
-                                   cudaStream_t stream) {
+                                   cudaStream_t stream, bool light) {
+    if (TRAV == CRT_TRAVERSAL_KD && light) {
+        if (stats)
+            k_wf_trace_light<true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+        else
+            k_wf_trace_light<false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+        return;
+    }
     if (stats)
         k_wf_trace<TRAV, true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
     else
@@ -381,8 +389,9 @@ inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, con
 }
 
 // `secondary` = the scene can spawn reflection / refraction rays at all (known from its materials on the host)
+// `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_light instead of k_wf_trace
 inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
-                                    uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches) {
+                                    uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves) {
     const int patches_x = (S.cam.width + 7) / 8, patches_y = (dp.rows + 3) / 4;
     const int P = patches_x * patches_y * 32;
     secondary = secondary && dp.max_ray_depth > 0;
@@ -393,7 +402,7 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     if ((e = cudaMemsetAsync(w.b.ctl, 0, sizeof(WfCtl), stream)) != cudaSuccess)
         return e;
     const int levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
-    const int trace_blocks = w.sm_count * 8;
+    const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? CRT_L_MINBLOCKS : 8);
     int n = 0;
     if (traversal != CRT_TRAVERSAL_LITERAL) {
         const int rb = min(w.sm_count * 16, (P + kRaygenBlock - 1) / kRaygenBlock);
@@ -406,9 +415,9 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     for (int level = 0; level < levels; ++level) {
         const int tb = level == 0 ? min(trace_blocks, (P + kTraceBlock - 1) / kTraceBlock) : trace_blocks;
         if (traversal == CRT_TRAVERSAL_LITERAL)
-            wavefront_launch_trace<CRT_TRAVERSAL_LITERAL>(w, S, dp, stats, level, tb, counters, stream);
+            wavefront_launch_trace<CRT_TRAVERSAL_LITERAL>(w, S, dp, stats, level, tb, counters, stream, false);
         else
-            wavefront_launch_trace<CRT_TRAVERSAL_KD>(w, S, dp, stats, level, tb, counters, stream);
+            wavefront_launch_trace<CRT_TRAVERSAL_KD>(w, S, dp, stats, level, tb, counters, stream, light_leaves);
         const int sb = level == 0 ? min(w.sm_count * 32, (P + kShadeBlock - 1) / kShadeBlock) : w.sm_count * 8;
         k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
         n += 2;
