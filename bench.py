@@ -300,13 +300,20 @@ def run_ours(args):
     alg_bytes = (16 * counted["node_tests"] + 48 * counted["tri_tests"] + 16 * counted["rays"]) / n + 15.0 * W * rows_local
     k_ms = statistics.mean(kernel_ms) if kernel_ms else ms_per_step
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    traffic = None
-    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")  # dram__bytes_read+write per frame from the committed ncu --set full capture
+    traffic, issue = None, None
+    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")  # per frame, from the committed ncu --set full capture of the same kernels
     if os.path.exists(traffic_path):
-        traffic = json.load(open(traffic_path)).get(args.workload, {}).get("dram_bytes_per_frame")
+        prof = json.load(open(traffic_path)).get(args.workload, {})
+        traffic = prof.get("dram_bytes_per_frame")
+        if prof.get("warp_instructions_per_frame") and clocks and clocks.get("sm_mhz") and world == 1:
+            # the bound that actually binds (tree + triangles are L2 resident): issue slots = 148 SMs x 4 schedulers x f_SM
+            slots = 148 * 4 * clocks["sm_mhz"] * 1e6 * (k_ms * 1e-3)
+            issue = {"warp_instructions": prof["warp_instructions_per_frame"], "issue_slots": slots, "frac": prof["warp_instructions_per_frame"] / slots,
+                     "source": "smsp__inst_executed.sum of the trace launches in " + prof.get("source", "profiles/") + "; slots from the live kernel time and SM clock"}
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "kernel": "k_wf_trace (all bounce levels of one frame; raygen/shade/resolve are < 3 % of the frame)", "kernel_ms": k_ms, "peak_source": peak_src,
+                "kernel": "k_wf_trace_light (all bounce levels of one frame; raygen/shade/resolve are < 5 % of the frame)", "kernel_ms": k_ms, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes,
+                "issue": issue,
                 "per_ray": {"kd_nodes_visited": counted["node_tests"] / max(1, counted["rays"]), "triangle_tests": counted["tri_tests"] / max(1, counted["rays"])}}
 
     cpu = None

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "crt_scene_free", "crt_scene_last_error", "crt_render_params_default", "crt_cuda_device_count", "crt_cuda_create",
     "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_set_camera",
     "crt_cuda_render", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
-    "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm",
+    "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
 ]
 
 
@@ -127,6 +127,7 @@ def _load_library():
         "crt_cuda_primary_hits": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, P(RenderStats)]),
         "crt_cuda_primary_rays": (C.c_int, [vp, vp]),
         "crt_cuda_encode_ppm": (C.c_int, [vp, vp, C.c_size_t, P(C.c_size_t)]),
+        "crt_cuda_encode_ppm_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_size_t, P(C.c_size_t)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -295,6 +296,14 @@ class Renderer:
         self._check(lib.crt_cuda_encode_ppm(self._ctx, None, 0, C.byref(length)), "crt_cuda_encode_ppm")
         buf = C.create_string_buffer(length.value)
         self._check(lib.crt_cuda_encode_ppm(self._ctx, buf, length.value, C.byref(length)), "crt_cuda_encode_ppm")
+        return buf.raw[: length.value]
+
+    def encode_ppm_device(self, rgb8_ptr: int, width: int, height: int) -> bytes:
+        """P3 text of any quantised frame in device memory (e.g. the gathered frame on rank 0)"""
+        length = C.c_size_t()
+        self._check(lib.crt_cuda_encode_ppm_device(self._ctx, C.c_void_p(rgb8_ptr), width, height, None, 0, C.byref(length)), "crt_cuda_encode_ppm_device")
+        buf = C.create_string_buffer(length.value)
+        self._check(lib.crt_cuda_encode_ppm_device(self._ctx, C.c_void_p(rgb8_ptr), width, height, buf, length.value, C.byref(length)), "crt_cuda_encode_ppm_device")
         return buf.raw[: length.value]
 
     def close(self):

@@ -49,6 +49,20 @@ void prepare_device(const Scene &scene) { (void)device_scene(scene); }
 
 RenderBreakdown last_render_breakdown() { return g_breakdown; }
 
+bool write_ppm_device(const Scene &scene, std::ostream &os) {
+    if (!scene.device)
+        return false;
+    crt_cuda_ctx *ctx = scene.device->ctx;
+    size_t length = 0;
+    if (crt_cuda_encode_ppm(ctx, nullptr, 0, &length) != CRT_OK)
+        return false;
+    std::string text(length, '\0');
+    if (crt_cuda_encode_ppm(ctx, text.data(), text.size(), &length) != CRT_OK)
+        return false;
+    os.write(text.data(), std::streamsize(length));
+    return true;
+}
+
 Image render_image(const Scene &scene, const RendererSettings &settings) {
     using clock = std::chrono::steady_clock;
     const auto t0 = clock::now();

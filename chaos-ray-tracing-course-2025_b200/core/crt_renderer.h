@@ -1,6 +1,7 @@
 #pragma once
 // The operator boundary, same signature as the reference (src/core/crt_renderer.h:10-27).
 #include <cstdint>
+#include <ostream>
 
 #include "crt_scene.h"
 
@@ -29,6 +30,10 @@ Image render_image(const Scene &scene, const RendererSettings &settings);
 
 // Optional: flatten + upload now (e.g. right after loading) so the first render_image carries no setup cost.
 void prepare_device(const Scene &scene);
+
+// P3 text (crt::write_ppm's bytes, src/core/crt_image_ppm.cpp:9-23) of the frame the last render_image of `scene`
+// left on the device, formatted by the GPU (csrc/crt_ppm.cuh).  False when the scene has no rendered frame.
+bool write_ppm_device(const Scene &scene, std::ostream &os);
 
 // timings of the last render_image on this thread, for the CLI's optional breakdown ($CRT_STATS=1)
 struct RenderBreakdown {

@@ -9,6 +9,7 @@
 
 #include "crt_kernels.cuh"
 #include "crt_wavefront.cuh"
+#include "crt_ppm.cuh"
 
 using namespace crtdev;
 
@@ -510,10 +511,56 @@ int crt_cuda_primary_hits(crt_cuda_ctx *ctx, int traversal, int32_t *tri_id, flo
     return CRT_OK;
 }
 
+int crt_cuda_encode_ppm_device(crt_cuda_ctx *ctx, const void *rgb8_dev, int width, int height, char *text_out, size_t capacity, size_t *length) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!rgb8_dev || width <= 0 || height <= 0)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm needs a device frame with positive dimensions");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    PpmHeader header{};
+    header.length = std::snprintf(header.text, sizeof header.text, "P3\n%d %d\n255\n", width, height);
+    const size_t pixels = size_t(width) * size_t(height);
+    const int n_blocks = int((pixels + kPpmBlockPixels - 1) / kPpmBlockPixels);
+    if (size_t(n_blocks) + 1 > ctx->d_scan_cap) {
+        cudaFree(ctx->d_scan);
+        ctx->d_scan = nullptr, ctx->d_scan_cap = 0;
+        CRT_CK(ctx, cudaMalloc(&ctx->d_scan, (size_t(n_blocks) + 1) * sizeof(unsigned long long)));
+        ctx->d_scan_cap = size_t(n_blocks) + 1;
+    }
+    const uint8_t *rgb8 = static_cast<const uint8_t *>(rgb8_dev);
+    k_ppm_lengths<<<n_blocks, kPpmThreads, 0, ctx->stream>>>(rgb8, pixels, width, ctx->d_scan);
+    k_ppm_scan<<<1, 1024, 0, ctx->stream>>>(ctx->d_scan, n_blocks);
+    unsigned long long body = 0;
+    CRT_CK(ctx, cudaMemcpyAsync(&body, ctx->d_scan + n_blocks, sizeof body, cudaMemcpyDeviceToHost, ctx->stream));
+    CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    const size_t total = size_t(header.length) + size_t(body);
+    if (length)
+        *length = total;
+    if (!text_out)
+        return CRT_OK;
+    if (capacity < total)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm: text buffer too small (query the length with text_out = NULL)");
+    if (total + 16 > ctx->d_text_cap) {
+        cudaFree(ctx->d_text);
+        ctx->d_text = nullptr, ctx->d_text_cap = 0;
+        CRT_CK(ctx, cudaMalloc(&ctx->d_text, total + 16));
+        ctx->d_text_cap = total + 16;
+    }
+    k_ppm_format<<<n_blocks, kPpmThreads, 0, ctx->stream>>>(rgb8, pixels, width, ctx->d_scan, header, ctx->d_text);
+    CRT_CK(ctx, cudaGetLastError());
+    CRT_CK(ctx, cudaMemcpyAsync(text_out, ctx->d_text, total, cudaMemcpyDeviceToHost, ctx->stream));
+    CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
 int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size_t *length) {
     if (!ctx)
         return CRT_ERR_INVALID;
-    return fail(ctx, CRT_ERR_INVALID, "crt_cuda_encode_ppm: not built yet");
+    if (!ctx->d_rgb8 || ctx->last_width <= 0 || ctx->last_rows <= 0)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm: no frame has been rendered on this context");
+    if (ctx->last_params.world > 1)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm: this context holds only its own row bands; encode the gathered frame with crt_cuda_encode_ppm_device");
+    return crt_cuda_encode_ppm_device(ctx, ctx->d_rgb8, ctx->last_width, ctx->last_rows, text_out, capacity, length);
 }
 
 #ifdef CRT_DEBUG_TAIL

@@ -69,6 +69,8 @@ struct __align__(16) TraceWarpShared {
 // shared memory ([entry][lane]: conflict-free), older ones are spilled to local memory and rarely read back.
 constexpr uint32_t kFlagBit = 0x80000000u; // entry pushed for a ray lying IN the split plane: its interval starts at 0
 
+constexpr int kPopAgain = -2;
+
 struct TraceWalker {
     float tmin, tmax, root_tmax;
     int node; // node to visit next, or -1 when the walk is finished
@@ -143,6 +145,35 @@ struct TraceWalker {
             }
         }
         if (STATS)
+            ++cn.node_tests;
+    }
+
+    // ONE pop attempt, straight-line (the light-leaf kernel calls it once per step slot instead of looping): node =
+    // the next subtree, -1 = the walk is over, kPopAgain = that entry was pruned, try the next one
+    template <bool STATS, class WS>
+    __device__ __forceinline__ void pop_once(WS &ws, unsigned lane, float best_t, Counters &cn) {
+        if (sp == 0) {
+            node = -1;
+            return;
+        }
+        --sp;
+        uint2 e = ws.stack[sp & (kWin - 1)][lane];
+        float below = __uint_as_float(ws.stack[(sp - 1) & (kWin - 1)][lane].y);
+        if (sp <= lo) { // rare: the entry or the one below it was spilled
+            if (sp < lo)
+                e = spill[sp], lo = sp;
+            if (sp > 0)
+                below = __uint_as_float(entry_at(ws, lane, sp - 1).y);
+        }
+        tmax = sp == 0 ? root_tmax : below;
+        const bool flag = (e.x & kFlagBit) != 0u;
+        flagged -= flag ? 1 : 0;
+        tmin = flag ? 0.0f : __uint_as_float(e.y);
+        const bool pruned = !flag & (tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best_t);
+        node = pruned ? kPopAgain : int(e.x & ~kFlagBit);
+        if (pruned & (flagged == 0) & (tmin - (fabsf(tmin) * 1e-3f + 1e-4f) > best_t)) // see pop(): everything below is pruned too
+            sp = 0, lo = 0, node = -1;
+        if (STATS && !pruned)
             ++cn.node_tests;
     }
 

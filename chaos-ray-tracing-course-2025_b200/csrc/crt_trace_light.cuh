@@ -17,7 +17,7 @@
 namespace crtdev {
 
 #ifndef CRT_L_STEPS
-#define CRT_L_STEPS 4
+#define CRT_L_STEPS 6
 #endif
 #ifndef CRT_L_TRIGGER
 #define CRT_L_TRIGGER 16
@@ -108,37 +108,38 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
         // ---- walk: up to CRT_L_STEPS node visits per lane; a leaf is parked and the walk goes on (speculatively: the
         //      leaf's triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong)
         bool blocked = false;
-        if (my >= 0 && w.node >= 0) {
+        if (my >= 0 && w.node != -1) {
             const float best_t = __uint_as_float(unsigned(ws.best[lane] >> 32));
 #pragma unroll
             for (int k = 0; k < CRT_L_STEPS; ++k) {
-                if (w.node < 0 || blocked)
+                if (w.node == -1 || blocked)
                     break;
-                const int4 n = __ldg(&S.kd_nodes[w.node]);
-                bool need_pop;
-                if (n.w == 3) {
-                    if (p1_count == 0) {
-                        if (p0_count == 0)
-                            p0_first = n.y, p0_count = n.z;
-                        else
-                            p1_first = n.y, p1_count = n.z;
-                        need_pop = true;
+                bool need_pop = w.node == kPopAgain;
+                if (!need_pop) {
+                    const int4 n = __ldg(&S.kd_nodes[w.node]);
+                    if (n.w == 3) {
+                        if (p1_count == 0) {
+                            if (p0_count == 0)
+                                p0_first = n.y, p0_count = n.z;
+                            else
+                                p1_first = n.y, p1_count = n.z;
+                            need_pop = true;
+                        } else {
+                            blocked = true; // both slots taken: wait for the test phase below
+                        }
                     } else {
-                        blocked = true; // both slots taken: wait for the test phase below
-                        need_pop = false;
+                        w.step<STATS>(ws, lane, n, best_t, cn);
+                        need_pop = w.node < 0;
                     }
-                } else {
-                    w.step<STATS>(ws, lane, n, best_t, cn);
-                    need_pop = w.node < 0;
                 }
                 if (need_pop)
-                    w.pop<STATS>(ws, lane, best_t, cn);
+                    w.pop_once<STATS>(ws, lane, best_t, cn);
             }
         }
         // ---- test phase: all parked leaves of all lanes at once
         const unsigned parked = __ballot_sync(full, p0_count > 0);
-        const unsigned walkers = __ballot_sync(full, my >= 0 && w.node >= 0 && !blocked);
-        const unsigned waiting = __ballot_sync(full, my >= 0 && w.node < 0 && p0_count > 0);
+        const unsigned walkers = __ballot_sync(full, my >= 0 && w.node != -1 && !blocked);
+        const unsigned waiting = __ballot_sync(full, my >= 0 && w.node == -1 && p0_count > 0);
         const bool fire = parked != 0u && (__popc(parked) >= CRT_L_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_L_WAITERS);
         if (fire) {
             const int mine = p0_count + p1_count;
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
             p0_count = 0, p1_count = 0;
         }
         // ---- retire: walk over and nothing parked
-        if (my >= 0 && w.node < 0 && p0_count == 0) {
+        if (my >= 0 && w.node == -1 && p0_count == 0) {
             Hit h{ kInf, -1 };
             if (live) {
                 const unsigned long long key = ws.best[lane];

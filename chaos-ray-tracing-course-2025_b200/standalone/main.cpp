@@ -5,6 +5,7 @@
 #include <filesystem>
 #include <fstream>
 #include <iostream>
+#include <string_view>
 
 #include "core/crt_image_ppm.h"
 #include "core/crt_json.h"
@@ -49,6 +50,14 @@ int main(int argc, char *argv[]) {
         std::cerr << "{\"gpu_ms\": " << b.gpu_ms << ", \"kernel_launches\": " << b.kernel_launches << ", \"render_image_s\": " << b.total_s << "}\n";
     }
 
-    crt::write_ppm(image, output);
+    // the frame is still on the device: the GPU formats the P3 text (same bytes as crt::write_ppm); CRT_PPM=host keeps
+    // the host encoder, which is also what any caller-modified Image goes through
+    const char *ppm = std::getenv("CRT_PPM");
+    if (ppm && std::string_view(ppm) == "host") {
+        crt::write_ppm(image, output);
+    } else if (!crt::write_ppm_device(*scene, output)) {
+        std::cerr << "Error: Could not encode the frame on the device\n";
+        return 1;
+    }
     return 0;
 }

@@ -213,6 +213,9 @@ int crt_cuda_primary_rays(crt_cuda_ctx *ctx, float *rays_out);
 /* P3 text encoding of the last frame on the device (crt_image_ppm.cpp:9-23), byte-exact.
  * Returns the byte count in *length; text_out may be NULL to query the size. */
 int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size_t *length);
+/* same for any quantised frame in device memory (width*height*3 bytes, row 0 = top), e.g. the frame rank 0 holds
+ * after the band gather of a multi-GPU render */
+int crt_cuda_encode_ppm_device(crt_cuda_ctx *ctx, const void *rgb8_dev, int width, int height, char *text_out, size_t capacity, size_t *length);
 
 #ifdef __cplusplus
 }
