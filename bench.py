@@ -219,15 +219,20 @@ def run_ours(args):
         dist.all_reduce(local_rays)
     job_rays_per_step = float(local_rays.item())  # all ranks together: one frame (stills) or N frames (animation)
 
-    gather = None
+    gather, peer = None, None
     if world > 1 and not frame_parallel:
-        gather = D.BandGather(W, H, band_rows, 3, device)
+        if args.gather == "peer":
+            peer = D.PeerFrame(renderer, W, H, device)  # bands are pushed into rank 0's frame over NVLink (crt_push.cuh)
+        else:
+            gather = D.BandGather(W, H, band_rows, 3, device)  # NCCL gather + un-interleave on rank 0
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
 
     def device_step(step):
         renderer.set_camera(camera_for(step))
         renderer.render_device(params)
-        if gather is not None:
+        if peer is not None:
+            peer.push()
+        elif gather is not None:
             _, rgb8_ptr, w, rows = renderer.device_framebuffer()
             gather.gather(D.wrap_device_bytes(rgb8_ptr, w * rows * 3, device))
 
@@ -327,13 +332,13 @@ def run_ours(args):
     line = {"metric": "Mrays/s (primary+secondary)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if frame_parallel else "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "traversal": "kd", "pipeline": args.pipeline, "partition": ("frames round-robin" if frame_parallel else f"row bands of {band_rows}, gather of u8 rgb to rank 0") if world > 1 else "single GPU",
+            "config": {"workload": desc, "traversal": "kd", "pipeline": args.pipeline, "partition": ("frames round-robin" if frame_parallel else f"row bands of {band_rows}, " + ("pushed into rank 0's frame by peer stores over NVLink + 1-element all-reduce as the barrier" if args.gather == "peer" else "NCCL gather of u8 rgb to rank 0")) if world > 1 else "single GPU",
                        "l2": "256 MiB flush between timed steps", "rays_per_step": job_rays_per_step, "scene_load_s": t_load, "scene_upload_s": t_upload,
                        "scene_bytes": int(flat.n_triangles * 64 + flat.n_nodes * 48 + flat.n_refs * 4)},
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 72 + 56, "d2h_bytes_per_step": rows_local * W * 12,
                     "ms_per_step": t_e2e / e2e_steps * 1e3},
-            "gpu_launches": kernel_launches * args.steps}
+            "gpu_launches": (kernel_launches + (1 if peer is not None else 0)) * args.steps}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -348,6 +353,7 @@ def main():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1 stills: how the row bands reach rank 0")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

@@ -30,6 +30,7 @@ EXPORTED_SYMBOLS = [
     "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_set_camera",
     "crt_cuda_render", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
     "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
+    "crt_cuda_frame_create", "crt_cuda_frame_open", "crt_cuda_frame_attach", "crt_cuda_frame_pointer", "crt_cuda_push_bands",
 ]
 
 
@@ -128,6 +129,11 @@ def _load_library():
         "crt_cuda_primary_rays": (C.c_int, [vp, vp]),
         "crt_cuda_encode_ppm": (C.c_int, [vp, vp, C.c_size_t, P(C.c_size_t)]),
         "crt_cuda_encode_ppm_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_size_t, P(C.c_size_t)]),
+        "crt_cuda_frame_create": (C.c_int, [vp, C.c_int, C.c_int, vp]),
+        "crt_cuda_frame_open": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+        "crt_cuda_frame_attach": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+        "crt_cuda_frame_pointer": (C.c_int, [vp, P(vp), P(C.c_int), P(C.c_int)]),
+        "crt_cuda_push_bands": (C.c_int, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -297,6 +303,26 @@ class Renderer:
         buf = C.create_string_buffer(length.value)
         self._check(lib.crt_cuda_encode_ppm(self._ctx, buf, length.value, C.byref(length)), "crt_cuda_encode_ppm")
         return buf.raw[: length.value]
+
+    # ---- multi-GPU stills: the frame on rank 0 that every rank pushes its row bands into (include/crt_cuda.h)
+    def frame_create(self, width: int, height: int) -> bytes:
+        handle = C.create_string_buffer(64)
+        self._check(lib.crt_cuda_frame_create(self._ctx, width, height, handle), "crt_cuda_frame_create")
+        return handle.raw
+
+    def frame_open(self, handle: bytes, width: int, height: int):
+        self._check(lib.crt_cuda_frame_open(self._ctx, C.create_string_buffer(handle, 64), width, height), "crt_cuda_frame_open")
+
+    def frame_attach(self, frame_ptr: int, width: int, height: int):
+        self._check(lib.crt_cuda_frame_attach(self._ctx, C.c_void_p(frame_ptr), width, height), "crt_cuda_frame_attach")
+
+    def frame_pointer(self):
+        ptr, w, h = C.c_void_p(), C.c_int(), C.c_int()
+        self._check(lib.crt_cuda_frame_pointer(self._ctx, C.byref(ptr), C.byref(w), C.byref(h)), "crt_cuda_frame_pointer")
+        return ptr.value, w.value, h.value
+
+    def push_bands(self):
+        self._check(lib.crt_cuda_push_bands(self._ctx), "crt_cuda_push_bands")
 
     def encode_ppm_device(self, rgb8_ptr: int, width: int, height: int) -> bytes:
         """P3 text of any quantised frame in device memory (e.g. the gathered frame on rank 0)"""

@@ -4,12 +4,14 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <string>
 #include <vector>
 
 #include "crt_kernels.cuh"
 #include "crt_wavefront.cuh"
 #include "crt_ppm.cuh"
+#include "crt_push.cuh"
 
 using namespace crtdev;
 
@@ -40,6 +42,10 @@ struct crt_cuda_ctx {
 
     WavefrontState wf; // ray queues of the wavefront pipeline (crt_wavefront.cuh)
 
+    uint8_t *frame = nullptr; // full quantised frame the row bands are pushed into (own allocation on rank 0, peer mapping elsewhere)
+    int frame_w = 0, frame_h = 0;
+    int frame_kind = 0;       // 0 none, 1 own cudaMalloc, 2 cudaIpcOpenMemHandle mapping, 3 caller's pointer
+
     char *d_text = nullptr; // PPM text
     size_t d_text_cap = 0;
     unsigned long long *d_scan = nullptr;
@@ -62,6 +68,14 @@ thread_local std::string g_create_error;
 int fail(crt_cuda_ctx *ctx, int code, const char *what) {
     ctx->error = what;
     return code;
+}
+
+void release_frame(crt_cuda_ctx *ctx) {
+    if (ctx->frame_kind == 1)
+        cudaFree(ctx->frame);
+    else if (ctx->frame_kind == 2)
+        cudaIpcCloseMemHandle(ctx->frame);
+    ctx->frame = nullptr, ctx->frame_kind = 0, ctx->frame_w = 0, ctx->frame_h = 0;
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -256,6 +270,7 @@ void crt_cuda_destroy(crt_cuda_ctx *ctx) {
     cudaFree(ctx->d_rgb8);
     cudaFree(ctx->d_counters);
     cudaFreeHost(ctx->h_counters);
+    release_frame(ctx);
     cudaFree(ctx->d_text);
     cudaFree(ctx->d_scan);
     if (ctx->ev_begin)
@@ -508,6 +523,86 @@ int crt_cuda_primary_hits(crt_cuda_ctx *ctx, int traversal, int32_t *tri_id, flo
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end);
     fill_stats(ctx, stats, ms);
+    return CRT_OK;
+}
+
+int crt_cuda_frame_create(crt_cuda_ctx *ctx, int width, int height, unsigned char handle_out[CRT_IPC_HANDLE_BYTES]) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (width <= 0 || height <= 0)
+        return fail(ctx, CRT_ERR_INVALID, "frame_create: non-positive size");
+    static_assert(sizeof(cudaIpcMemHandle_t) == CRT_IPC_HANDLE_BYTES, "handle size");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    release_frame(ctx);
+    CRT_CK(ctx, cudaMalloc(&ctx->frame, size_t(width) * size_t(height) * 3));
+    ctx->frame_kind = 1, ctx->frame_w = width, ctx->frame_h = height;
+    if (handle_out) {
+        cudaIpcMemHandle_t h;
+        CRT_CK(ctx, cudaIpcGetMemHandle(&h, ctx->frame));
+        std::memcpy(handle_out, &h, sizeof h);
+    }
+    return CRT_OK;
+}
+
+int crt_cuda_frame_open(crt_cuda_ctx *ctx, const unsigned char handle[CRT_IPC_HANDLE_BYTES], int width, int height) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!handle || width <= 0 || height <= 0)
+        return fail(ctx, CRT_ERR_INVALID, "frame_open: handle and a positive size are required");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    release_frame(ctx);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    void *mapped = nullptr;
+    CRT_CK(ctx, cudaIpcOpenMemHandle(&mapped, h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->frame = static_cast<uint8_t *>(mapped);
+    ctx->frame_kind = 2, ctx->frame_w = width, ctx->frame_h = height;
+    return CRT_OK;
+}
+
+int crt_cuda_frame_attach(crt_cuda_ctx *ctx, void *frame_dev, int width, int height) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!frame_dev || width <= 0 || height <= 0)
+        return fail(ctx, CRT_ERR_INVALID, "frame_attach: pointer and a positive size are required");
+    release_frame(ctx);
+    ctx->frame = static_cast<uint8_t *>(frame_dev);
+    ctx->frame_kind = 3, ctx->frame_w = width, ctx->frame_h = height;
+    return CRT_OK;
+}
+
+int crt_cuda_frame_pointer(crt_cuda_ctx *ctx, void **frame_dev, int *width, int *height) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (frame_dev)
+        *frame_dev = ctx->frame;
+    if (width)
+        *width = ctx->frame_w;
+    if (height)
+        *height = ctx->frame_h;
+    return CRT_OK;
+}
+
+int crt_cuda_push_bands(crt_cuda_ctx *ctx) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!ctx->frame)
+        return fail(ctx, CRT_ERR_INVALID, "push_bands: no frame (crt_cuda_frame_create / _open / _attach first)");
+    if (!ctx->d_rgb8 || ctx->last_width != ctx->frame_w || ctx->scene.cam.height != ctx->frame_h)
+        return fail(ctx, CRT_ERR_INVALID, "push_bands: the last rendered frame does not match the frame's size");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    const DParams dp = device_params(ctx->last_params, ctx->frame_h);
+    if (dp.rows <= 0)
+        return CRT_OK;
+    const size_t row_bytes = size_t(ctx->frame_w) * 3;
+    const bool vec = row_bytes % 16 == 0 && reinterpret_cast<uintptr_t>(ctx->frame) % 16 == 0 && reinterpret_cast<uintptr_t>(ctx->d_rgb8) % 16 == 0;
+    const size_t units = vec ? row_bytes / 16 : row_bytes;
+    const int blocks = int(std::min<size_t>((size_t(dp.rows) * units + 255) / 256, size_t(148 * 8)));
+    if (vec)
+        k_push_bands<uint4><<<blocks, 256, 0, ctx->stream>>>(reinterpret_cast<const uint4 *>(ctx->d_rgb8), reinterpret_cast<uint4 *>(ctx->frame), dp.rows, int(units), dp);
+    else
+        k_push_bands<uint8_t><<<blocks, 256, 0, ctx->stream>>>(ctx->d_rgb8, ctx->frame, dp.rows, int(units), dp);
+    CRT_CK(ctx, cudaGetLastError());
     return CRT_OK;
 }
 

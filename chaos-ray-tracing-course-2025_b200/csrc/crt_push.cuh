@@ -1,0 +1,24 @@
+// Multi-GPU stills, the exchange step: every rank PUSHES its row bands straight into the frame that
+// lives in rank 0's memory -- plain 16-byte stores through a peer mapping (NVLink / NVSwitch), with the band
+// un-interleave folded into the address computation.  There is no staging buffer, no gather collective and no
+// separate scatter kernel on rank 0; the only collective left is the completion barrier the caller issues.
+#pragma once
+
+#include <cstdint>
+
+#include "crt_device.cuh"
+
+namespace crtdev {
+
+// src: this rank's compact rows (rows_local x row_bytes); dst: the full frame (height x row_bytes) on rank 0
+template <typename Unit>
+__global__ void __launch_bounds__(256) k_push_bands(const Unit *__restrict__ src, Unit *__restrict__ dst, int rows_local, int units_per_row, DParams p) {
+    const size_t total = size_t(rows_local) * size_t(units_per_row);
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+        const int ly = int(i / size_t(units_per_row));
+        const int u = int(i - size_t(ly) * size_t(units_per_row));
+        dst[size_t(global_row(p, ly)) * size_t(units_per_row) + u] = src[i];
+    }
+}
+
+} // namespace crtdev

@@ -70,6 +70,7 @@ struct __align__(16) TraceWarpShared {
 constexpr uint32_t kFlagBit = 0x80000000u; // entry pushed for a ray lying IN the split plane: its interval starts at 0
 
 constexpr int kPopAgain = -2;
+constexpr int kStolenNode = 0x7FFFFFFF; // stack entry whose subtree a helper lane has taken over
 
 struct TraceWalker {
     float tmin, tmax, root_tmax;
@@ -171,6 +172,8 @@ struct TraceWalker {
         tmin = flag ? 0.0f : __uint_as_float(e.y);
         const bool pruned = !flag & (tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best_t);
         node = pruned ? kPopAgain : int(e.x & ~kFlagBit);
+        if (node == kStolenNode) // the subtree was handed to a helper lane (k_wf_trace_light)
+            node = kPopAgain;
         if (pruned & (flagged == 0) & (tmin - (fabsf(tmin) * 1e-3f + 1e-4f) > best_t)) // see pop(): everything below is pruned too
             sp = 0, lo = 0, node = -1;
         if (STATS && !pruned)
@@ -182,11 +185,17 @@ struct TraceWalker {
     // conditional.
     template <bool STATS, class WS>
     __device__ __forceinline__ bool step(WS &ws, unsigned lane, const int4 n, float best_t, Counters &cn) {
+        return step<STATS>(ws, lane, lane, n, best_t, cn);
+    }
+
+    // `src` = the lane whose ray this walk belongs to (a helper lane walks a subtree of another lane's ray)
+    template <bool STATS, class WS>
+    __device__ __forceinline__ bool step(WS &ws, unsigned lane, unsigned src, const int4 n, float best_t, Counters &cn, const int4 *prefetch = nullptr) {
         if (n.w == 3)
             return true;
         const int axis = n.w;
         const float split = __int_as_float(n.x);
-        const float oa = ws.ray[axis][lane], da = ws.ray[3 + axis][lane], ia = ws.ray[6 + axis][lane];
+        const float oa = ws.ray[axis][src], da = ws.ray[3 + axis][src], ia = ws.ray[6 + axis][src];
         const bool below = (oa < split) | ((oa == split) & (da <= 0.0f));
         const int near = below ? n.y : n.z, far = below ? n.z : n.y;
         const float tp = (split - oa) * ia;
@@ -200,6 +209,10 @@ struct TraceWalker {
         const bool go_far = far_only | (both & !has_near);
         const int next = go_far ? far : near;
         push_if(ws, lane, do_push, uint32_t(far) | (in_plane ? kFlagBit : 0u), in_plane ? tmax : tp);
+#ifdef CRT_PREFETCH_FAR
+        if (prefetch && do_push) // the far child is loaded many steps from now: have it in L2 by then
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(prefetch + far));
+#endif
         flagged += (do_push & in_plane) ? 1 : 0;
         tmax = (do_push & !in_plane) ? fminf(tmax, tp) : tmax;
         tmin = (both & !has_near & has_far & !in_plane) ? fmaxf(tmin, tp) : tmin;

@@ -36,6 +36,7 @@ struct __align__(16) LightWarpShared {
     float ray[9][32];            // origin xyz, direction xyz, 1/direction xyz of each lane's ray
     unsigned long long best[32]; // (float bits of t) << 32 | triangle index
     uint2 stack[kWin][32];       // {node | kFlagBit, entry distance bits}
+    int helpers[32];             // lanes currently walking a stolen subtree of this lane's ray
 };
 
 template <bool STATS>
@@ -58,18 +59,30 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
     bool live = false;
     int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0; // parked leaves
     bool exhausted = false;
+    unsigned src = lane;  // lane whose ray I am walking: myself, or the owner of the subtree I took over
+    bool helper = false;  // I own no ray, I walk a stolen subtree of lane `src`'s ray
+    int stolen = 0;       // bottom entries of my stack that helpers have taken over (tombstones)
+#ifdef CRT_DEBUG_TAIL
+    unsigned rounds = 0;
+    unsigned long long t_start, t_exhausted = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
     for (;;) {
         // ---- refill idle lanes from the level's queue
-        const unsigned busy = __ballot_sync(full, my >= 0);
+        const unsigned busy = __ballot_sync(full, my >= 0 || helper);
         if (!exhausted && __popc(busy) < CRT_L_REFILL) {
             const unsigned idle = ~busy;
             int base = 0;
             if (lane == 0)
                 base = atomicAdd(&ctl->fetch[level], __popc(idle));
             base = __shfl_sync(full, base, 0);
-            if (base + __popc(idle) >= total)
+            if (base + __popc(idle) >= total) {
                 exhausted = true;
-            if (my < 0) {
+#ifdef CRT_DEBUG_TAIL
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_exhausted));
+#endif
+            }
+            if (my < 0 && !helper) {
                 const int i = base + __popc(idle & lt_mask);
                 if (i < total) {
                     V3 o, d, inv;
@@ -90,6 +103,9 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                         }
                     }
                     my = i;
+                    src = lane;
+                    stolen = 0;
+                    ws.helpers[lane] = 0;
                     live = t_enter <= t_exit;
                     w.node = -1;
                     if (live) {
@@ -100,16 +116,63 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
             }
             __syncwarp();
         }
-        if (__ballot_sync(full, my >= 0) == 0u) {
+        if (__ballot_sync(full, my >= 0 || helper) == 0u) {
             if (exhausted)
                 break;
             continue;
         }
+        // ---- the queue is empty and some lanes have nothing to do: they take over pending subtrees of the lanes that
+        //      are still walking (the BOTTOM stack entry = the farthest, usually largest piece of the remaining path).
+        //      A bounce level ends with its longest ray; a skimming ray crosses ~1000 cells one dependent load at a
+        //      time, and this spreads that walk over the warp.  The victim's entry becomes a tombstone (its entry
+        //      distance still bounds the entry above it); hits merge through the owner's ws.best as always.
+        if (exhausted) {
+            const unsigned thieves = __ballot_sync(full, my < 0 && !helper);
+            stolen = min(stolen, w.sp); // entries below `stolen` are tombstones; popping past them frees the slots
+            const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
+            const bool can_give = (my >= 0 || helper) && w.node != -1 && w.lo == 0 && w.sp - stolen >= 2 && lowest < uint32_t(kStolenNode);
+            const unsigned victims = __ballot_sync(full, can_give);
+            if (thieves != 0u && victims != 0u) {
+                const int pairs = min(__popc(thieves), __popc(victims));
+                const bool thief = my < 0 && !helper;
+                const int rank = thief ? __popc(thieves & lt_mask) : (can_give ? __popc(victims & lt_mask) : 32);
+                const bool paired = rank < pairs;
+                const unsigned v = (paired && thief) ? __fns(victims, 0, rank + 1) : lane; // the rank-th victim
+                const unsigned v_src = __shfl_sync(full, src, v);
+                const float v_root_exit = __shfl_sync(full, w.root_tmax, v);
+                const int v_stolen = __shfl_sync(full, stolen, v);
+                if (paired && thief) {
+                    const uint2 e = ws.stack[v_stolen & (kWin - 1)][v];
+                    // exit distance of that entry = entry distance of the one below it (tombstones keep theirs)
+                    const float exit_t = v_stolen == 0 ? v_root_exit : __uint_as_float(ws.stack[(v_stolen - 1) & (kWin - 1)][v].y);
+                    helper = true;
+                    src = v_src;
+                    stolen = 0;
+                    w.sp = 0, w.lo = 0, w.flagged = 0;
+                    w.node = int(e.x);
+                    w.tmin = __uint_as_float(e.y);
+                    w.tmax = exit_t, w.root_tmax = exit_t;
+                    atomicAdd(&ws.helpers[v_src], 1);
+                    if (STATS)
+                        ++cn.node_tests;
+                }
+                __syncwarp();
+                if (paired && !thief) {
+                    ws.stack[stolen & (kWin - 1)][lane].x = uint32_t(kStolenNode);
+                    ++stolen;
+                }
+                __syncwarp();
+            }
+        }
         // ---- walk: up to CRT_L_STEPS node visits per lane; a leaf is parked and the walk goes on (speculatively: the
         //      leaf's triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong)
+#ifdef CRT_DEBUG_TAIL
+        if (my >= 0)
+            ++rounds;
+#endif
         bool blocked = false;
-        if (my >= 0 && w.node != -1) {
-            const float best_t = __uint_as_float(unsigned(ws.best[lane] >> 32));
+        if ((my >= 0 || helper) && w.node != -1) {
+            const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
 #pragma unroll
             for (int k = 0; k < CRT_L_STEPS; ++k) {
                 if (w.node == -1 || blocked)
@@ -128,7 +191,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                             blocked = true; // both slots taken: wait for the test phase below
                         }
                     } else {
-                        w.step<STATS>(ws, lane, n, best_t, cn);
+                        w.step<STATS>(ws, lane, src, n, best_t, cn, S.kd_nodes);
                         need_pop = w.node < 0;
                     }
                 }
@@ -138,8 +201,8 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
         }
         // ---- test phase: all parked leaves of all lanes at once
         const unsigned parked = __ballot_sync(full, p0_count > 0);
-        const unsigned walkers = __ballot_sync(full, my >= 0 && w.node != -1 && !blocked);
-        const unsigned waiting = __ballot_sync(full, my >= 0 && w.node == -1 && p0_count > 0);
+        const unsigned walkers = __ballot_sync(full, (my >= 0 || helper) && w.node != -1 && !blocked);
+        const unsigned waiting = __ballot_sync(full, (my >= 0 || helper) && w.node == -1 && p0_count > 0);
         const bool fire = parked != 0u && (__popc(parked) >= CRT_L_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_L_WAITERS);
         if (fire) {
             const int mine = p0_count + p1_count;
@@ -166,6 +229,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                 const int o_excl = __shfl_sync(full, excl, owner);
                 const int o_first0 = __shfl_sync(full, p0_first, owner), o_count0 = __shfl_sync(full, p0_count, owner);
                 const int o_first1 = __shfl_sync(full, p1_first, owner);
+                owner = int(__shfl_sync(full, src, owner)); // a helper's leaves are tested against the ray it helps
                 if (item < items) {
                     const int k = item - o_excl;
                     const uint32_t ref = __ldg(&S.kd_refs[k < o_count0 ? o_first0 + k : o_first1 + (k - o_count0)]);
@@ -184,8 +248,14 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
             __syncwarp();
             p0_count = 0, p1_count = 0;
         }
-        // ---- retire: walk over and nothing parked
-        if (my >= 0 && w.node == -1 && p0_count == 0) {
+        // ---- retire: walk over and nothing parked; helpers first, then the rays nobody is helping any more
+        if (helper && w.node == -1 && p0_count == 0) {
+            atomicSub(&ws.helpers[src], 1);
+            helper = false;
+            src = lane;
+        }
+        __syncwarp();
+        if (my >= 0 && w.node == -1 && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0)) {
             Hit h{ kInf, -1 };
             if (live) {
                 const unsigned long long key = ws.best[lane];
@@ -193,9 +263,25 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                 h.tri = int(unsigned(key & 0xffffffffull));
             }
             b.hit[node_id] = make_float2(h.t, __int_as_float(h.tri));
+#ifdef CRT_DEBUG_TAIL
+            atomicMax(&g_tail[level][0], (unsigned long long)rounds);
+            atomicAdd(&g_tail[level][1], (unsigned long long)rounds);
+            atomicAdd(&g_tail[level][2 + (rounds ? 32 - __clz(rounds) : 0)], 1ull);
+            rounds = 0;
+#endif
             my = -1;
         }
     }
+#ifdef CRT_DEBUG_TAIL
+    if (lane == 0) {
+        unsigned long long t_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        atomicMax(&g_tail[level][30], t_exhausted - t_start); // ns until this warp found the queue empty
+        atomicMax(&g_tail[level][31], t_end - t_start);       // ns until this warp left
+        atomicAdd(&g_tail[level][32], t_end - t_start);       // sum over warps
+        atomicAdd(&g_tail[level][33], 1ull);
+    }
+#endif
     if (STATS)
         flush_counters(cn, counters);
 }

@@ -77,3 +77,39 @@ class BandGather:
             if k:
                 frame.index_copy_(0, self.index[r], self.recv[r][: k * self.row_bytes].view(k, self.row_bytes))
         return self.frame
+
+
+class PeerFrame:
+    """The exchange step without a gather: rank 0 owns the full quantised frame, every rank's push kernel stores its
+    row bands into it through a CUDA-IPC peer mapping (NVLink), un-interleaving on the way (csrc/crt_push.cuh).
+    torch.distributed only ships the 64-byte handle once and provides the completion barrier (a 1-element all-reduce
+    on the render stream, so nothing blocks the host)."""
+
+    def __init__(self, renderer, width: int, height: int, device, group=None):
+        self.renderer, self.group = renderer, group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.width, self.height = width, height
+        self.device = torch.device(device)
+        handle = torch.zeros(64, dtype=torch.uint8, device=self.device)
+        if self.rank == 0:
+            raw = renderer.frame_create(width, height)
+            handle.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        if self.world > 1:
+            dist.broadcast(handle, src=0, group=group)
+            if self.rank != 0:
+                renderer.frame_open(bytes(handle.cpu().numpy().tobytes()), width, height)
+        self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+
+    def push(self):
+        """enqueue this rank's bands -> rank 0's frame, then the completion barrier (asynchronous on the stream)"""
+        self.renderer.push_bands()
+        if self.world > 1:
+            dist.all_reduce(self.flag, group=self.group)
+
+    def frame(self) -> torch.Tensor | None:
+        """the assembled frame (uint8 [H, W, 3]) on rank 0 once the stream has passed the barrier"""
+        if self.rank != 0:
+            return None
+        ptr, w, h = self.renderer.frame_pointer()
+        return wrap_device_bytes(ptr, w * h * 3, self.device).view(h, w, 3)

@@ -210,6 +210,21 @@ int crt_cuda_primary_hits(crt_cuda_ctx *ctx, int traversal, int32_t *tri_id, flo
 /* Parity hook for ray generation (crt_camera.cpp:7-35): 6 floats per pixel (origin, direction) */
 int crt_cuda_primary_rays(crt_cuda_ctx *ctx, float *rays_out);
 
+/* ------------------------------------------------------------------------------------------------
+ * Multi-GPU stills (replaces the shared `buffer[y*W + x]` the reference's bucket threads write,
+ * crt_renderer.cpp:171-196): rank 0 owns the full quantised frame, every rank pushes its row bands into it with
+ * direct peer stores (NVLink), un-interleaving on the way.  One process per GPU: rank 0 calls frame_create and ships
+ * the 64-byte handle to the other ranks (any transport), they call frame_open.  One process driving several GPUs, or
+ * several contexts on one GPU: frame_attach with the raw device pointer.  After crt_cuda_render_device, every rank
+ * calls crt_cuda_push_bands (asynchronous on the stream); the caller then synchronises the ranks (a barrier) and
+ * rank 0 reads the frame (crt_cuda_frame_pointer, crt_cuda_encode_ppm_device). */
+#define CRT_IPC_HANDLE_BYTES 64
+int crt_cuda_frame_create(crt_cuda_ctx *ctx, int width, int height, unsigned char handle_out[CRT_IPC_HANDLE_BYTES]);
+int crt_cuda_frame_open(crt_cuda_ctx *ctx, const unsigned char handle[CRT_IPC_HANDLE_BYTES], int width, int height);
+int crt_cuda_frame_attach(crt_cuda_ctx *ctx, void *frame_dev, int width, int height);
+int crt_cuda_frame_pointer(crt_cuda_ctx *ctx, void **frame_dev, int *width, int *height);
+int crt_cuda_push_bands(crt_cuda_ctx *ctx);
+
 /* P3 text encoding of the last frame on the device (crt_image_ppm.cpp:9-23), byte-exact.
  * Returns the byte count in *length; text_out may be NULL to query the size. */
 int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size_t *length);

@@ -180,3 +180,33 @@ def test_band_ownership_reassembles_the_frame(crt, ot, renderer):
             out[rows] = part
             seen[rows] += 1
         assert (seen == 1).all() and same_bits(out, full)
+
+
+def test_pushed_bands_assemble_the_frame_on_rank0(crt, ot, renderer):
+    """multi-GPU stills without a gather: every rank's push kernel stores its bands into rank 0's frame (here: two and
+    three contexts on one GPU sharing the frame by pointer; across processes the same pointer comes from CUDA IPC)"""
+    for size in ((320, 181), (322, 90)):  # row bytes divisible by 16 (vector path) and not (byte path)
+        scene, flat = load(crt, ot, "15-01-conclusion/scene1.crtscene", size)
+        renderer.upload(flat)
+        _, full8, _ = renderer.render(crt.default_params())
+        for world, band in ((2, 8), (3, 5)):
+            ranks = [crt.Renderer(0) for _ in range(world)]
+            try:
+                ranks[0].frame_create(size[0], size[1])
+                ptr, w, h = ranks[0].frame_pointer()
+                assert (w, h) == size
+                for r in ranks[1:]:
+                    r.frame_attach(ptr, w, h)
+                for k, r in enumerate(ranks):
+                    r.upload(flat)
+                    r.render_device(crt.default_params(rank=k, world=world, band_rows=band))
+                    r.push_bands()
+                    r.synchronize()
+                import torch
+                from crt_b200 import distributed as D
+                got = D.wrap_device_bytes(ptr, w * h * 3, torch.device("cuda", 0)).cpu().numpy().reshape(h, w, 3)
+                assert np.array_equal(got, full8)
+                assert ranks[0].encode_ppm_device(ptr, w, h) == renderer.encode_ppm()
+            finally:
+                for r in ranks:
+                    r.close()

@@ -19,4 +19,5 @@ print("gpu_ms", st["gpu_ms"])
 for lvl in range(depth + 1):
     row = buf[lvl * 40:(lvl + 1) * 40]
     n = sum(row[2:])
-    print(f"level {lvl}: rays {n} max rounds {row[0]} mean {row[1] / max(n, 1):.1f} log2 histogram {[int(v) for v in row[2:20]]}")
+    print(f"level {lvl}: rays {n} max rounds {row[0]} mean {row[1] / max(n, 1):.1f} log2 histogram {[int(v) for v in row[2:20]]}"
+          f"  | us until queue empty (max over warps) {row[30] / 1e3:.0f}, until last warp left {row[31] / 1e3:.0f}, mean warp lifetime {row[32] / max(row[33], 1) / 1e3:.0f}")
