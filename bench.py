@@ -43,6 +43,7 @@ WORKLOADS = {
     "c4-diffuse": ("synthetic 1002528-triangle height field, diffuse, 3840x2160, max_ray_depth 8, 1 point light", 3840, 2160, 8, (1920, 1080)),
     "c1": ("scenes/14-01-acceleration-tree/scene1 (== 13-01-optimizations/scene0), 1920x1080, defaults", 1920, 1080, 3, (1920, 1080)),
     "c3": ("scenes/15-01-conclusion/scene1 at 3840x2160, defaults", 3840, 2160, 3, (1920, 1080)),
+    "c3-gi": ("scenes/15-01-conclusion/scene2 (GI on, refractive + reflective) at 2160x2160, defaults", 2160, 2160, 3, (360, 360)),
     "c5": ("scenes/11-01-refractive/scene8 1920x1080, one orbit frame per step (240-frame orbit, frame k -> rank k % N)", 1920, 1080, 3, (1920, 1080)),
 }
 
@@ -56,7 +57,7 @@ def scene_text(workload: str, size=None) -> tuple[str, str]:
         from crt_b200 import scenes
         w, h = size or WORKLOADS[workload][1:3]
         return scenes.height_field_scene(708, w, h, "diffuse" if workload.endswith("diffuse") else "reflective"), ""
-    rel = {"c1": "14-01-acceleration-tree/scene1.crtscene", "c3": "15-01-conclusion/scene1.crtscene", "c5": "11-01-refractive/scene8.crtscene"}[workload]
+    rel = {"c1": "14-01-acceleration-tree/scene1.crtscene", "c3": "15-01-conclusion/scene1.crtscene", "c3-gi": "15-01-conclusion/scene2.crtscene", "c5": "11-01-refractive/scene8.crtscene"}[workload]
     w, h = size or WORKLOADS[workload][1:3]
     return ot.scene_variant(rel, w, h), os.path.dirname(ot.scene_file(rel))
 
@@ -188,7 +189,10 @@ def run_ours(args):
         a = flat.arrays()
         center = (np.array(list(flat.root_min)) + np.array(list(flat.root_max))) / 2
         orbit = scenes.orbit_cameras(list(flat.camera.position), list(flat.camera.rotation), center, 240)
-    frame_parallel = orbit is not None  # animation: whole frames per rank, no exchange
+    # N > 1: whole frames per rank with no exchange ("frames": animation-style, frame k -> rank k % N; for the still
+    # workloads every frame uses the workload's camera, so each GPU does exactly the N = 1 work -> weak scaling), or one
+    # frame cut into interleaved row bands that are pushed to rank 0 ("tiles": strong scaling; also measured below)
+    frame_parallel = orbit is not None or (world > 1 and args.partition == "frames")
     band_rows = 8
     pipeline = {"auto": crt.PIPELINE_AUTO, "mega": crt.PIPELINE_MEGAKERNEL, "wavefront": crt.PIPELINE_WAVEFRONT}[args.pipeline]
     common = dict(max_ray_depth=depth, traversal=crt.TRAVERSAL_KD, pipeline=pipeline)
@@ -286,6 +290,43 @@ def run_ours(args):
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     t_e2e = float(t_e2e.item())
 
+    # --- N > 1, still workloads: the tile-sharded single frame as well (strong scaling, exchange inside the timed step)
+    tiles = None
+    if world > 1 and orbit is None:
+        t_params = crt.default_params(**common, rank=rank, world=world, band_rows=band_rows)
+        t_peer = D.PeerFrame(renderer, W, H, device) if args.gather == "peer" else None
+        t_gather = None if t_peer else D.BandGather(W, H, band_rows, 3, device)
+
+        def tile_step():
+            renderer.render_device(t_params)
+            if t_peer is not None:
+                t_peer.push()
+            else:
+                _, rgb8_ptr, w, rows = renderer.device_framebuffer()
+                t_gather.gather(D.wrap_device_bytes(rgb8_ptr, w * rows * 3, device))
+
+        renderer.set_camera(camera_for(0))
+        for _ in range(3):
+            tile_step()
+        torch.cuda.synchronize(device)
+        dist.barrier()
+        t_steps = min(args.steps, 20)
+        tb = [torch.cuda.Event(enable_timing=True) for _ in range(t_steps)]
+        te = [torch.cuda.Event(enable_timing=True) for _ in range(t_steps)]
+        for s in range(t_steps):
+            flush.fill_(s & 0xFF)
+            tb[s].record(stream)
+            tile_step()
+            te[s].record(stream)
+        torch.cuda.synchronize(device)
+        dist.barrier()
+        t_ms = torch.tensor([sum(a.elapsed_time(c) for a, c in zip(tb, te)) / t_steps], dtype=torch.float64, device=device)
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        frame_rays = job_rays_per_step / world if frame_parallel else job_rays_per_step
+        tiles = {"ms_per_frame": float(t_ms.item()), "value": frame_rays / (float(t_ms.item()) * 1e-3) / 1e6, "unit": "Mrays/s", "scaling": "strong",
+                 "partition": f"one frame, interleaved row bands of {band_rows}, " + ("pushed into rank 0's frame by peer stores over NVLink (crt_push.cuh) + a 1-element all-reduce as the barrier"
+                                                                                       if args.gather == "peer" else "NCCL gather of u8 rgb to rank 0")}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -332,10 +373,10 @@ def run_ours(args):
     line = {"metric": "Mrays/s (primary+secondary)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if frame_parallel else "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "traversal": "kd", "pipeline": args.pipeline, "partition": ("frames round-robin" if frame_parallel else f"row bands of {band_rows}, " + ("pushed into rank 0's frame by peer stores over NVLink + 1-element all-reduce as the barrier" if args.gather == "peer" else "NCCL gather of u8 rgb to rank 0")) if world > 1 else "single GPU",
+            "config": {"workload": desc, "traversal": "kd", "pipeline": args.pipeline, "partition": ("whole frames per rank (frame k -> rank k % N), no exchange" if frame_parallel else f"row bands of {band_rows}, " + ("pushed into rank 0's frame by peer stores over NVLink + 1-element all-reduce as the barrier" if args.gather == "peer" else "NCCL gather of u8 rgb to rank 0")) if world > 1 else "single GPU",
                        "l2": "256 MiB flush between timed steps", "rays_per_step": job_rays_per_step, "scene_load_s": t_load, "scene_upload_s": t_upload,
                        "scene_bytes": int(flat.n_triangles * 64 + flat.n_nodes * 48 + flat.n_refs * 4)},
-            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "tiles": tiles, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 72 + 56, "d2h_bytes_per_step": rows_local * W * 12,
                     "ms_per_step": t_e2e / e2e_steps * 1e3},
             "gpu_launches": (kernel_launches + (1 if peer is not None else 0)) * args.steps}
@@ -353,6 +394,7 @@ def main():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
+    ap.add_argument("--partition", default="frames", choices=["frames", "tiles"], help="N > 1 stills: whole frames per rank (weak) or one frame in row bands (strong)")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1 stills: how the row bands reach rank 0")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
