@@ -10,6 +10,7 @@
 
 #include "crt_kernels.cuh"
 #include "crt_wavefront.cuh"
+#include "crt_persistent.cuh"
 #include "crt_ppm.cuh"
 #include "crt_push.cuh"
 
@@ -17,6 +18,7 @@ using namespace crtdev;
 
 struct crt_cuda_ctx {
     int device = 0;
+    int sm_count = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::string error;
 
@@ -40,6 +42,7 @@ struct crt_cuda_ctx {
     int last_width = 0, last_rows = 0, last_launches = 0;
     bool last_stats = false;
 
+    PersistCtl *d_pctl = nullptr; // pixel cursor of the persistent pipeline (crt_persistent.cuh)
     WavefrontState wf; // ray queues of the wavefront pipeline (crt_wavefront.cuh)
 
     uint8_t *frame = nullptr; // full quantised frame the row bands are pushed into (own allocation on rank 0, peer mapping elsewhere)
@@ -176,10 +179,42 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         int pipeline = params->pipeline;
         const bool needs_mega = (ctx->scene.gi_on && dp.gi_rays > 0) || params->shadows;
         if (pipeline == CRT_PIPELINE_AUTO)
-            pipeline = (needs_mega || !kWavefrontReady) ? CRT_PIPELINE_MEGAKERNEL : CRT_PIPELINE_WAVEFRONT;
-        if (pipeline == CRT_PIPELINE_WAVEFRONT && needs_mega)
+            // GI keeps a pixel's recursion on one lane (RNG order): the persistent kernel; shadow rays and the
+            // verification traversal: the per-pixel megakernel; everything else: the wavefront
+            pipeline = params->shadows || (needs_mega && params->traversal != CRT_TRAVERSAL_KD) ? CRT_PIPELINE_MEGAKERNEL
+                       : needs_mega                                                              ? CRT_PIPELINE_PERSISTENT
+                                                                                                 : CRT_PIPELINE_WAVEFRONT;
+        if (pipeline == CRT_PIPELINE_PERSISTENT) {
+            if (params->shadows)
+                return fail(ctx, CRT_ERR_INVALID, "the persistent pipeline does not trace shadow rays; use CRT_PIPELINE_MEGAKERNEL");
+            if (params->traversal != CRT_TRAVERSAL_KD)
+                return fail(ctx, CRT_ERR_INVALID, "the persistent pipeline walks the k-d walk tree only (CRT_TRAVERSAL_KD)");
+            if (!ctx->d_pctl)
+                CRT_CK(ctx, cudaMalloc(&ctx->d_pctl, sizeof(PersistCtl)));
+            CRT_CK(ctx, cudaMemsetAsync(ctx->d_pctl, 0, sizeof(PersistCtl), ctx->stream));
+            const int patches_x = (W + 7) / 8, patches_y = (dp.rows + 3) / 4;
+            const int n_slots = patches_x * patches_y * 32;
+            cudaDeviceProp prop;
+            if (ctx->sm_count == 0) {
+                CRT_CK(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+                ctx->sm_count = prop.multiProcessorCount;
+            }
+            const int blocks = std::min(ctx->sm_count * CRT_P_MINBLOCKS, (n_slots + kTraceBlock - 1) / kTraceBlock);
+            const bool gi = ctx->scene.gi_on && dp.gi_rays > 0;
+            if (gi && stats)
+                k_render_persistent<true, true><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+            else if (gi)
+                k_render_persistent<false, true><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+            else if (stats)
+                k_render_persistent<true, false><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+            else
+                k_render_persistent<false, false><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+            ctx->last_launches = 1;
+        } else if (pipeline == CRT_PIPELINE_WAVEFRONT && needs_mega)
             return fail(ctx, CRT_ERR_INVALID, "the wavefront pipeline does not handle GI or shadow rays; use CRT_PIPELINE_MEGAKERNEL");
-        if (pipeline == CRT_PIPELINE_WAVEFRONT) {
+        if (pipeline == CRT_PIPELINE_PERSISTENT) {
+            // launched above
+        } else if (pipeline == CRT_PIPELINE_WAVEFRONT) {
             int launches = 0;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
                                              ctx->d_counters, ctx->stream, &launches, ctx->light_leaves);
@@ -271,6 +306,7 @@ void crt_cuda_destroy(crt_cuda_ctx *ctx) {
     cudaFree(ctx->d_counters);
     cudaFreeHost(ctx->h_counters);
     release_frame(ctx);
+    cudaFree(ctx->d_pctl);
     cudaFree(ctx->d_text);
     cudaFree(ctx->d_scan);
     if (ctx->ev_begin)

@@ -210,3 +210,25 @@ def test_pushed_bands_assemble_the_frame_on_rank0(crt, ot, renderer):
             finally:
                 for r in ranks:
                     r.close()
+
+
+@pytest.mark.parametrize("rel", ["15-01-conclusion/scene2.crtscene", "15-01-conclusion/scene1.crtscene", "11-01-refractive/scene8.crtscene",
+                                 "11-01-refractive/scene5.crtscene", "12-01-textures/scene4.crtscene", "14-01-acceleration-tree/scene0.crtscene"])
+def test_persistent_pipeline_equals_the_other_pipelines_bit_for_bit(crt, ot, renderer, rel):
+    """CRT_PIPELINE_PERSISTENT (one kernel, a lane keeps its pixel through the recursion, warp-cooperative walk) runs the
+    same arithmetic in the same nesting as the megakernel / wavefront: identical float framebuffers, identical ray
+    counts, GI (one PCG32 stream per pixel) included; and it meets the oracle bars."""
+    scene, flat = load(crt, ot, rel)
+    renderer.upload(flat)
+    for depth in (3, 0, 5):
+        auto, auto8, st_a = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1))
+        pers, pers8, st_p = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1, pipeline=crt.PIPELINE_PERSISTENT))
+        assert same_bits(auto, pers) and np.array_equal(auto8, pers8)
+        assert st_a["rays"] == st_p["rays"] and st_a["rays_by_depth"] == st_p["rays_by_depth"]
+    want = ot.port_render(flat, crt.default_params(), primary=False)
+    pers, pers8, _ = renderer.render(crt.default_params(pipeline=crt.PIPELINE_PERSISTENT))
+    assert ppm_ok_fraction(pers8, want["rgb8"]) >= 0.999
+    # ragged band ownership goes through the same pixel-slot mapping
+    part, _, _ = renderer.render(crt.default_params(pipeline=crt.PIPELINE_PERSISTENT, rank=1, world=3, band_rows=5))
+    rows = crt.Renderer.owned_rows(pers.shape[0], 1, 3, 5)
+    assert same_bits(part, pers[rows])
