@@ -20,7 +20,7 @@ LIB_PATH = os.environ.get("CRT_B200_LIB") or os.path.join(_HERE, "lib", "libcrt_
 CRT_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_IO, ERR_PARSE, ERR_NO_DEVICE = -1, -2, -3, -4, -5
 TRAVERSAL_LITERAL, TRAVERSAL_KD, TRAVERSAL_BRUTE = 0, 1, 2
-PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_PERSISTENT = 0, 1, 2, 3
+PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_PERSISTENT, PIPELINE_HYBRID = 0, 1, 2, 3, 4
 REF_CULL_BIT = 0x80000000
 
 # every symbol include/crt_cuda.h declares (tests check that the library exports each of them)

@@ -150,6 +150,21 @@ void launch_mega(crt_cuda_ctx *ctx, const DParams &dp, bool stats, dim3 grid) {
         k_render_mega<TRAV, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
 }
 
+template <bool SEEDED>
+void launch_persistent(crt_cuda_ctx *ctx, const DParams &dp, bool stats, bool gi, int blocks, int patches_x, int n_slots) {
+#define CRT_LAUNCH_P(ST, G) \
+    k_render_persistent<ST, G, SEEDED><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, ctx->wf.b)
+    if (gi && stats)
+        CRT_LAUNCH_P(true, true);
+    else if (gi)
+        CRT_LAUNCH_P(false, true);
+    else if (stats)
+        CRT_LAUNCH_P(true, false);
+    else
+        CRT_LAUNCH_P(false, false);
+#undef CRT_LAUNCH_P
+}
+
 // enqueue one frame on ctx->stream, bracketed by the timing events
 int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     if (!ctx->have_scene)
@@ -199,21 +214,34 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
                 CRT_CK(ctx, cudaGetDeviceProperties(&prop, ctx->device));
                 ctx->sm_count = prop.multiProcessorCount;
             }
-            const int blocks = std::min(ctx->sm_count * CRT_P_MINBLOCKS, (n_slots + kTraceBlock - 1) / kTraceBlock);
-            const bool gi = ctx->scene.gi_on && dp.gi_rays > 0;
-            if (gi && stats)
-                k_render_persistent<true, true><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
-            else if (gi)
-                k_render_persistent<false, true><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
-            else if (stats)
-                k_render_persistent<true, false><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
-            else
-                k_render_persistent<false, false><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
+            const bool gi_frame = ctx->scene.gi_on && dp.gi_rays > 0;
+            const int blocks = std::min(ctx->sm_count * (gi_frame ? CRT_P_MINBLOCKS_GI : CRT_P_MINBLOCKS), (n_slots + kTraceBlock - 1) / kTraceBlock);
+            launch_persistent<false>(ctx, dp, stats, gi_frame, blocks, patches_x, n_slots);
             ctx->last_launches = 1;
         } else if (pipeline == CRT_PIPELINE_WAVEFRONT && needs_mega)
             return fail(ctx, CRT_ERR_INVALID, "the wavefront pipeline does not handle GI or shadow rays; use CRT_PIPELINE_MEGAKERNEL");
         if (pipeline == CRT_PIPELINE_PERSISTENT) {
             // launched above
+        } else if (pipeline == CRT_PIPELINE_HYBRID) {
+            // primary level as wavefront kernels (dense, coherent), every deeper level in ONE persistent kernel
+            if (needs_mega || params->traversal != CRT_TRAVERSAL_KD)
+                return fail(ctx, CRT_ERR_INVALID, "the hybrid pipeline handles neither GI, shadow rays nor the literal traversal");
+            int launches = 0;
+            const bool deeper = ctx->has_secondary && dp.max_ray_depth > 0;
+            cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
+                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, true);
+            ctx->last_wavefront = true;
+            if (e != cudaSuccess)
+                return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
+            if (deeper) {
+                if (!ctx->d_pctl)
+                    CRT_CK(ctx, cudaMalloc(&ctx->d_pctl, sizeof(PersistCtl)));
+                CRT_CK(ctx, cudaMemsetAsync(ctx->d_pctl, 0, sizeof(PersistCtl), ctx->stream));
+                launch_persistent<true>(ctx, dp, stats, false, ctx->wf.sm_count * CRT_P_MINBLOCKS, 0, 0);
+                k_wf_resolve<<<ctx->wf.sm_count * 4, 256, 0, ctx->stream>>>(ctx->scene, dp, ctx->wf.b, 0, ctx->d_rgb, ctx->d_rgb8);
+                launches += 2;
+            }
+            ctx->last_launches = launches;
         } else if (pipeline == CRT_PIPELINE_WAVEFRONT) {
             int launches = 0;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,

@@ -17,7 +17,13 @@
 namespace crtdev {
 
 #ifndef CRT_P_MINBLOCKS
-#define CRT_P_MINBLOCKS 5
+#define CRT_P_MINBLOCKS 6
+#endif
+#ifndef CRT_P_MINBLOCKS_GI
+#define CRT_P_MINBLOCKS_GI 5 // the GI continuation (sinf / cosf, PCG state) needs ~90 registers
+#endif
+#ifndef CRT_P_PATIENCE
+#define CRT_P_PATIENCE 8
 #endif
 #ifndef CRT_P_SHADE_TRIGGER
 #define CRT_P_SHADE_TRIGGER 12
@@ -35,11 +41,17 @@ __device__ __forceinline__ bool persist_slot_pixel(int slot, int patches_x, int 
     return x < width && ly < rows;
 }
 
-template <bool STATS, bool GI>
-__global__ void __launch_bounds__(kTraceBlock, CRT_P_MINBLOCKS) k_render_persistent(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
-                                                                                    PersistCtl *__restrict__ ctl, int patches_x, int n_slots,
+// SEEDED: the work items are not pixels but the level-1 rays the wavefront's level-0 shade stage queued (hybrid
+// pipeline: the dense, coherent primary level runs as raygen / trace / shade kernels at full SIMD width, everything
+// deeper runs here).  A lane takes a level-1 ray, evaluates its whole subtree depth-first and stores the subtree's
+// colour in the level-1 node record, which the level-0 resolve kernel combines as before.
+template <bool STATS, bool GI, bool SEEDED>
+__global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_MINBLOCKS) k_render_persistent(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
+                                                                                    PersistCtl *__restrict__ ctl, int patches_x, int n_slots_arg,
                                                                                     float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
-                                                                                    Counters *__restrict__ counters) {
+                                                                                    Counters *__restrict__ counters, const __grid_constant__ WfBuffers b) {
+    const int n_slots = SEEDED ? b.ctl->count[1] : n_slots_arg;
+    const int base_depth = SEEDED ? 1 : 0;
     Counters cn{};
     __shared__ LightWarpShared shared[kTraceWarps];
     LightWarpShared &ws = shared[threadIdx.x >> 5];
@@ -81,8 +93,10 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_P_MINBLOCKS) k_render_persist
             if (ply < 0 && !helper) {
                 const int slot = base + __popc(idle & lt_mask);
                 int x, ly;
-                if (slot < n_slots && persist_slot_pixel(slot, patches_x, S.cam.width, P.rows, x, ly)) {
-                    px = x, ply = ly, depth = 0;
+                if (slot < n_slots && (SEEDED || persist_slot_pixel(slot, patches_x, S.cam.width, P.rows, x, ly))) {
+                    if (SEEDED)
+                        x = slot, ly = 0; // px = index of my level-1 ray
+                    px = x, ply = ly, depth = base_depth;
                     fresh = true, live = false;
                     src = lane, stolen = 0;
                     ws.helpers[lane] = 0;
@@ -232,7 +246,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_P_MINBLOCKS) k_render_persist
         const unsigned ready_m = __ballot_sync(full, ready);
         const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && w.node != -1);
         patience = ready_m != 0u ? patience + 1 : 0;
-        if (ready_m != 0u && (__popc(ready_m) >= CRT_P_SHADE_TRIGGER || walking_m == 0u || patience >= 4)) {
+        if (ready_m != 0u && (__popc(ready_m) >= CRT_P_SHADE_TRIGGER || walking_m == 0u || patience >= CRT_P_PATIENCE)) {
             patience = 0;
             if (ready) {
                 int act = 0; // 0: consume the finished query, 1: shade_ray(ray, depth) entry, 2: return c to the callers
@@ -240,11 +254,15 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_P_MINBLOCKS) k_render_persist
                 V3 c = mk(0.0f, 0.0f, 0.0f);
                 if (fresh) {
                     fresh = false;
-                    const int y = global_row(P, ply);
-                    if (GI)
-                        rng = make_pcg(uint32_t(px), uint32_t(y));
-                    ray = generate_ray(S.cam, px, y);
-                    depth = 0;
+                    if (SEEDED) {
+                        ray = Ray{ xyz(b.ray_o[px]), xyz(b.ray_d[px]) };
+                    } else {
+                        const int y = global_row(P, ply);
+                        if (GI)
+                            rng = make_pcg(uint32_t(px), uint32_t(y));
+                        ray = generate_ray(S.cam, px, y);
+                    }
+                    depth = base_depth;
                     act = 1;
                 }
                 for (;;) {
@@ -333,8 +351,11 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_P_MINBLOCKS) k_render_persist
                         continue;
                     }
                     // act == 2: return c to the callers (the frame stack is the recursion's return path)
-                    if (depth == 0) {
-                        write_pixel(S, rgb, rgb8, px, ply, c);
+                    if (depth == base_depth) {
+                        if (SEEDED)
+                            b.col[b.P + px] = make_float4(c.x, c.y, c.z, 0.0f);
+                        else
+                            write_pixel(S, rgb, rgb8, px, ply, c);
                         ply = -1;
                         break;
                     }

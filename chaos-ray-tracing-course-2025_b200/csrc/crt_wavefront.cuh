@@ -391,7 +391,8 @@ inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, con
 // `secondary` = the scene can spawn reflection / refraction rays at all (known from its materials on the host)
 // `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_light instead of k_wf_trace
 inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
-                                    uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves) {
+                                    uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves,
+                                    bool primary_level_only = false) {
     const int patches_x = (S.cam.width + 7) / 8, patches_y = (dp.rows + 3) / 4;
     const int P = patches_x * patches_y * 32;
     secondary = secondary && dp.max_ray_depth > 0;
@@ -401,7 +402,9 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     w.b.patches_x = patches_x;
     if ((e = cudaMemsetAsync(w.b.ctl, 0, sizeof(WfCtl), stream)) != cudaSuccess)
         return e;
-    const int levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
+    // primary_level_only (hybrid pipeline): raygen, trace and shade of level 0 only; the caller evaluates the queued
+    // level-1 rays' subtrees (k_render_persistent<SEEDED>) and then runs the level-0 resolve
+    const int levels = secondary && !primary_level_only ? int(dp.max_ray_depth) + 1 : 1;
     const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? CRT_L_MINBLOCKS : 8);
     int n = 0;
     if (traversal != CRT_TRAVERSAL_LITERAL) {

@@ -149,6 +149,7 @@ typedef struct crt_cuda_ctx crt_cuda_ctx;
 #define CRT_PIPELINE_AUTO 0      /* wavefront without GI, persistent with GI, megakernel for shadow rays / literal GI */
 #define CRT_PIPELINE_MEGAKERNEL 1 /* one thread per pixel evaluates the whole recursion depth-first     */
 #define CRT_PIPELINE_WAVEFRONT 2  /* ray queues + compaction between bounce stages (no GI)              */
+#define CRT_PIPELINE_HYBRID 4     /* primary level as wavefront kernels, all deeper levels in one persistent kernel (no GI) */
 #define CRT_PIPELINE_PERSISTENT 3 /* one persistent kernel: a lane keeps its pixel through the recursion, warp-cooperative walk (GI too) */
 
 /* crt::RendererSettings (src/core/crt_renderer.h:18-25) + the knobs that are new on this side */

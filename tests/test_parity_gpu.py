@@ -221,10 +221,16 @@ def test_persistent_pipeline_equals_the_other_pipelines_bit_for_bit(crt, ot, ren
     scene, flat = load(crt, ot, rel)
     renderer.upload(flat)
     for depth in (3, 0, 5):
-        auto, auto8, st_a = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1))
+        auto, auto8, st_a = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1, pipeline=crt.PIPELINE_MEGAKERNEL))
         pers, pers8, st_p = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1, pipeline=crt.PIPELINE_PERSISTENT))
         assert same_bits(auto, pers) and np.array_equal(auto8, pers8)
         assert st_a["rays"] == st_p["rays"] and st_a["rays_by_depth"] == st_p["rays_by_depth"]
+        dflt, _, _ = renderer.render(crt.default_params(max_ray_depth=depth))  # whatever CRT_PIPELINE_AUTO picks
+        assert same_bits(dflt, pers)
+        if not flat.gi_on:  # primary level as wavefront kernels + one persistent kernel for everything deeper
+            hyb, hyb8, st_h = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1, pipeline=crt.PIPELINE_HYBRID))
+            assert same_bits(hyb, pers) and np.array_equal(hyb8, pers8)
+            assert st_h["rays"] == st_p["rays"] and st_h["rays_by_depth"] == st_p["rays_by_depth"]
     want = ot.port_render(flat, crt.default_params(), primary=False)
     pers, pers8, _ = renderer.render(crt.default_params(pipeline=crt.PIPELINE_PERSISTENT))
     assert ppm_ok_fraction(pers8, want["rgb8"]) >= 0.999

@@ -22,7 +22,7 @@ scene = crt.Scene.load_json(text, root)
 r = crt.Renderer(0)
 flat = r.upload(scene)
 p = crt.default_params(max_ray_depth=depth, collect_stats=stats,
-                       pipeline={"auto": 0, "mega": 1, "wavefront": 2, "persistent": 3}[pipeline], traversal={"kd": 1, "literal": 0}[traversal])
+                       pipeline={"auto": 0, "mega": 1, "wavefront": 2, "persistent": 3, "hybrid": 4}[pipeline], traversal={"kd": 1, "literal": 0}[traversal])
 for i in range(frames):
     _, _, st = r.render(p, want_rgb=False, want_rgb8=False)
     print(workload, pipeline, traversal, "frame", i, {k: v for k, v in st.items() if v and k != "pad"})
