@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     auto no_shadow = [](V3, float) { return false; };
 
     TraceWalker w;
+    uint2 spill[kStack]; // stack entries below the shared-memory window
     w.node = -1, w.sp = 0, w.lo = 0, w.flagged = 0;
     // ---- pixel state
     int px = 0, ply = -1; // my pixel (local row), ply < 0 = no pixel
@@ -177,12 +178,12 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                             blocked = true; // both slots taken: wait for the test phase below
                         }
                     } else {
-                        w.step<STATS>(ws, lane, src, n, best_t, cn, S.kd_nodes);
+                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn, S.kd_nodes);
                         need_pop = w.node < 0;
                     }
                 }
                 if (need_pop)
-                    w.pop_once<STATS>(ws, lane, best_t, cn);
+                    w.pop_once<STATS>(ws, spill, lane, best_t, cn);
             }
         }
         // ---- test phase: all parked leaves of all lanes at once

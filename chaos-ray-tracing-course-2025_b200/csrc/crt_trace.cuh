@@ -76,7 +76,8 @@ struct TraceWalker {
     float tmin, tmax, root_tmax;
     int node; // node to visit next, or -1 when the walk is finished
     int sp, lo, flagged;
-    uint2 spill[kStack];
+    // the spilled entries live in a local array of the KERNEL (`spill`, kStack entries), not in this struct: a
+    // dynamically indexed member would force the whole walker -- node, sp, tmin, tmax -- into local memory
 
     // start a walk from a ray record (entry/exit of the root box and 1/direction come with the record)
     template <class WS>
@@ -93,7 +94,7 @@ struct TraceWalker {
 
     // the store happens whether or not anything is pushed (slot sp is free), only the count moves: no branch per push
     template <class WS>
-    __device__ __forceinline__ void push_if(WS &ws, unsigned lane, bool doit, uint32_t tagged_node, float entry) {
+    __device__ __forceinline__ void push_if(WS &ws, uint2 *spill, unsigned lane, bool doit, uint32_t tagged_node, float entry) {
         const bool full = sp - lo == kWin;
         if (doit & full) { // window full (rare): the oldest entry goes to local memory
             spill[lo] = ws.stack[lo & (kWin - 1)][lane];
@@ -105,13 +106,13 @@ struct TraceWalker {
     }
 
     template <class WS>
-    __device__ __forceinline__ uint2 entry_at(const WS &ws, unsigned lane, int i) const {
+    __device__ __forceinline__ uint2 entry_at(const WS &ws, const uint2 *spill, unsigned lane, int i) const {
         return i >= lo ? ws.stack[i & (kWin - 1)][lane] : spill[i];
     }
 
     // next pending subtree that can still hold a closer (or equal) hit; node = -1 when none is left
     template <bool STATS, class WS>
-    __device__ __forceinline__ void pop(WS &ws, unsigned lane, float best_t, Counters &cn) {
+    __device__ __forceinline__ void pop(WS &ws, uint2 *spill, unsigned lane, float best_t, Counters &cn) {
         for (;;) {
             if (sp == 0) {
                 node = -1;
@@ -124,7 +125,7 @@ struct TraceWalker {
                 if (sp < lo)
                     e = spill[sp], lo = sp;
                 if (sp > 0)
-                    below = __uint_as_float(entry_at(ws, lane, sp - 1).y);
+                    below = __uint_as_float(entry_at(ws, spill, lane, sp - 1).y);
             }
             tmax = sp == 0 ? root_tmax : below;
             node = int(e.x & ~kFlagBit);
@@ -152,7 +153,7 @@ struct TraceWalker {
     // ONE pop attempt, straight-line (the light-leaf kernel calls it once per step slot instead of looping): node =
     // the next subtree, -1 = the walk is over, kPopAgain = that entry was pruned, try the next one
     template <bool STATS, class WS>
-    __device__ __forceinline__ void pop_once(WS &ws, unsigned lane, float best_t, Counters &cn) {
+    __device__ __forceinline__ void pop_once(WS &ws, uint2 *spill, unsigned lane, float best_t, Counters &cn) {
         if (sp == 0) {
             node = -1;
             return;
@@ -164,7 +165,7 @@ struct TraceWalker {
             if (sp < lo)
                 e = spill[sp], lo = sp;
             if (sp > 0)
-                below = __uint_as_float(entry_at(ws, lane, sp - 1).y);
+                below = __uint_as_float(entry_at(ws, spill, lane, sp - 1).y);
         }
         tmax = sp == 0 ? root_tmax : below;
         const bool flag = (e.x & kFlagBit) != 0u;
@@ -184,13 +185,13 @@ struct TraceWalker {
     // the lanes of a warp, which sit at unrelated nodes, share one instruction stream; only the push and the pop stay
     // conditional.
     template <bool STATS, class WS>
-    __device__ __forceinline__ bool step(WS &ws, unsigned lane, const int4 n, float best_t, Counters &cn) {
-        return step<STATS>(ws, lane, lane, n, best_t, cn);
+    __device__ __forceinline__ bool step(WS &ws, uint2 *spill, unsigned lane, const int4 n, float best_t, Counters &cn) {
+        return step<STATS>(ws, spill, lane, lane, n, best_t, cn);
     }
 
     // `src` = the lane whose ray this walk belongs to (a helper lane walks a subtree of another lane's ray)
     template <bool STATS, class WS>
-    __device__ __forceinline__ bool step(WS &ws, unsigned lane, unsigned src, const int4 n, float best_t, Counters &cn, const int4 *prefetch = nullptr) {
+    __device__ __forceinline__ bool step(WS &ws, uint2 *spill, unsigned lane, unsigned src, const int4 n, float best_t, Counters &cn, const int4 *prefetch = nullptr) {
         if (n.w == 3)
             return true;
         const int axis = n.w;
@@ -208,7 +209,7 @@ struct TraceWalker {
         const bool do_push = both & has_near & has_far;
         const bool go_far = far_only | (both & !has_near);
         const int next = go_far ? far : near;
-        push_if(ws, lane, do_push, uint32_t(far) | (in_plane ? kFlagBit : 0u), in_plane ? tmax : tp);
+        push_if(ws, spill, lane, do_push, uint32_t(far) | (in_plane ? kFlagBit : 0u), in_plane ? tmax : tp);
 #ifdef CRT_PREFETCH_FAR
         if (prefetch && do_push) // the far child is loaded many steps from now: have it in L2 by then
             asm volatile("prefetch.global.L2 [%0];" ::"l"(prefetch + far));
@@ -310,6 +311,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
     const unsigned lt_mask = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
     TraceWalker w;
+    uint2 spill[kStack];
     w.node = -1, w.sp = 0, w.lo = 0, w.flagged = 0;
     int my = -1;                        // index of my ray within the level, -1 = idle
     int node_id = 0;                    // where my ray's hit record goes
@@ -469,10 +471,10 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
                         break;
                     n = __ldg(&S.kd_nodes[w.node]);
                 }
-                if (w.step<STATS>(ws, lane, n, best_t, cn))
+                if (w.step<STATS>(ws, spill, lane, n, best_t, cn))
                     leaf_first = n.y, leaf_count = n.z, w.node = -1;
                 if (w.node < 0) // leaf handed over, or an absent child: one pop site for both
-                    w.pop<STATS>(ws, lane, best_t, cn);
+                    w.pop<STATS>(ws, spill, lane, best_t, cn);
             }
         }
         // ---- f. retire: walk over, nothing left to gather, every candidate tested

@@ -53,6 +53,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
     const unsigned lt_mask = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
     TraceWalker w;
+    uint2 spill[kStack]; // stack entries below the shared-memory window
     w.node = -1, w.sp = 0, w.lo = 0, w.flagged = 0;
     int my = -1;      // index of my ray within the level, -1 = idle
     int node_id = 0;  // where my ray's hit record goes
@@ -191,12 +192,12 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                             blocked = true; // both slots taken: wait for the test phase below
                         }
                     } else {
-                        w.step<STATS>(ws, lane, src, n, best_t, cn, S.kd_nodes);
+                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn, S.kd_nodes);
                         need_pop = w.node < 0;
                     }
                 }
                 if (need_pop)
-                    w.pop_once<STATS>(ws, lane, best_t, cn);
+                    w.pop_once<STATS>(ws, spill, lane, best_t, cn);
             }
         }
         // ---- test phase: all parked leaves of all lanes at once
