@@ -70,7 +70,7 @@ class ClockSampler:
     def __init__(self, index: int):
         self.rows, self.proc = [], None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -194,7 +194,8 @@ def run_ours(args):
     # frame cut into interleaved row bands that are pushed to rank 0 ("tiles": strong scaling; also measured below)
     frame_parallel = orbit is not None or (world > 1 and args.partition == "frames")
     band_rows = 8
-    pipeline = {"auto": crt.PIPELINE_AUTO, "mega": crt.PIPELINE_MEGAKERNEL, "wavefront": crt.PIPELINE_WAVEFRONT}[args.pipeline]
+    pipeline = {"auto": crt.PIPELINE_AUTO, "mega": crt.PIPELINE_MEGAKERNEL, "wavefront": crt.PIPELINE_WAVEFRONT, "persistent": crt.PIPELINE_PERSISTENT,
+                "hybrid": crt.PIPELINE_HYBRID}[args.pipeline]
     common = dict(max_ray_depth=depth, traversal=crt.TRAVERSAL_KD, pipeline=pipeline)
     part = dict(rank=0, world=1) if frame_parallel else dict(rank=rank, world=world, band_rows=band_rows)
     params = crt.default_params(**common, **part)
@@ -393,7 +394,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
+    ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront", "persistent", "hybrid"])
     ap.add_argument("--partition", default="frames", choices=["frames", "tiles"], help="N > 1 stills: whole frames per rank (weak) or one frame in row bands (strong)")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1 stills: how the row bands reach rank 0")
     args = ap.parse_args()

@@ -25,8 +25,11 @@ namespace crtdev {
 #ifndef CRT_P_PATIENCE
 #define CRT_P_PATIENCE 8
 #endif
+#ifndef CRT_P_STEPS
+#define CRT_P_STEPS 6
+#endif
 #ifndef CRT_P_SHADE_TRIGGER
-#define CRT_P_SHADE_TRIGGER 12
+#define CRT_P_SHADE_TRIGGER 20
 #endif
 
 struct PersistCtl {
@@ -161,7 +164,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         if ((ply >= 0 || helper) && w.node != -1) { // fresh pixels have w.node == -1
             const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
 #pragma unroll
-            for (int k = 0; k < CRT_L_STEPS; ++k) {
+            for (int k = 0; k < CRT_P_STEPS; ++k) {
                 if (w.node == -1 || blocked)
                     break;
                 bool need_pop = w.node == kPopAgain;

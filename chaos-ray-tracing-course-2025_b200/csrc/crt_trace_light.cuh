@@ -17,7 +17,7 @@
 namespace crtdev {
 
 #ifndef CRT_L_STEPS
-#define CRT_L_STEPS 6
+#define CRT_L_STEPS 8
 #endif
 #ifndef CRT_L_TRIGGER
 #define CRT_L_TRIGGER 16
@@ -26,7 +26,7 @@ namespace crtdev {
 #define CRT_L_WAITERS 6
 #endif
 #ifndef CRT_L_MINBLOCKS
-#define CRT_L_MINBLOCKS 8
+#define CRT_L_MINBLOCKS 9
 #endif
 #ifndef CRT_L_REFILL
 #define CRT_L_REFILL 25
