@@ -18,9 +18,9 @@ struct KdBuildStats {
 
 struct KdBuildParams {
     float c_node{ 1.0f };  // cost of one node step of the trace kernel (the unit)
-    float c_leaf{ 2.0f };  // fixed cost of handing a leaf to the candidate list
-    float c_tri{ 2.8f };   // cost per gathered + tested triangle
-    float empty_bonus{ 0.85f }; // a split that cuts away empty space is favoured a little (the far side is never stepped)
+    float c_leaf{ 1.0f };  // fixed cost of parking a leaf for the next test phase
+    float c_tri{ 1.5f };   // cost per tested triangle (swept on B200 with k_wf_trace_light, tools/sah_sweep.sh)
+    float empty_bonus{ 1.0f }; // < 1 favours splits that cut away empty space; the sweep on B200 found no gain from it
     int max_depth{ 44 };   // device stack: fast_max_depth + 2 <= kStack (48)
     int exact_below{ 96 }; // nodes with at most this many triangles sweep every triangle bound; larger ones use bins
     int bins{ 64 };
