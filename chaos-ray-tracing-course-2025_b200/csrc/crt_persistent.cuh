@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
             for (int k = 0; k < CRT_P_STEPS; ++k) {
                 if (w.node == -1 || blocked)
                     break;
-                bool need_pop = w.node == kPopAgain;
+                bool need_pop = w.prune_at_visit(best_t);
                 if (!need_pop) {
                     const int4 n = __ldg(&S.kd_nodes[w.node]);
                     if (n.w == 3) {
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                     }
                 }
                 if (need_pop)
-                    w.pop_once<STATS>(ws, spill, lane, best_t, cn);
+                    w.pop_fast<STATS>(ws, spill, lane, cn);
             }
         }
         // ---- test phase: all parked leaves of all lanes at once
