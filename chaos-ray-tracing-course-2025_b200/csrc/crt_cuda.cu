@@ -199,6 +199,12 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
             pipeline = params->shadows || (needs_mega && params->traversal != CRT_TRAVERSAL_KD) ? CRT_PIPELINE_MEGAKERNEL
                        : needs_mega                                                              ? CRT_PIPELINE_PERSISTENT
                                                                                                  : CRT_PIPELINE_WAVEFRONT;
+            // deep recursions and band-sharded frames end in many small bounce levels, each lasting as long as its
+            // longest walk: there everything below the primary level goes to ONE persistent kernel (measured on B200:
+            // C4 depth 8 3.51 -> 3.36 ms, its 2-GPU band-sharded frame 2.47 -> 2.01 ms; depth-3 scenes prefer the levels)
+            if (pipeline == CRT_PIPELINE_WAVEFRONT && params->traversal == CRT_TRAVERSAL_KD && ctx->light_leaves && ctx->has_secondary &&
+                (dp.max_ray_depth >= 5 || params->world > 1))
+                pipeline = CRT_PIPELINE_HYBRID;
         if (pipeline == CRT_PIPELINE_PERSISTENT) {
             if (params->shadows)
                 return fail(ctx, CRT_ERR_INVALID, "the persistent pipeline does not trace shadow rays; use CRT_PIPELINE_MEGAKERNEL");

@@ -17,10 +17,13 @@
 namespace crtdev {
 
 #ifndef CRT_P_MINBLOCKS
-#define CRT_P_MINBLOCKS 6
+#define CRT_P_MINBLOCKS 7
 #endif
 #ifndef CRT_P_MINBLOCKS_GI
-#define CRT_P_MINBLOCKS_GI 5 // the GI continuation (sinf / cosf, PCG state) needs ~90 registers
+#define CRT_P_MINBLOCKS_GI 8 // 64 registers: the GI continuation (sinf / cosf, PCG state) spills a few values, the walk does not
+#endif
+#ifndef CRT_P_PATIENCE_GI
+#define CRT_P_PATIENCE_GI 16
 #endif
 #ifndef CRT_P_PATIENCE
 #define CRT_P_PATIENCE 8
@@ -28,8 +31,14 @@ namespace crtdev {
 #ifndef CRT_P_STEPS
 #define CRT_P_STEPS 6
 #endif
+#ifndef CRT_P_STEPS_GI
+#define CRT_P_STEPS_GI 2 // GI queries are short (a diffuse bounce ends at the next surface): more frequent phase changes pay
+#endif
+#ifndef CRT_P_SHADE_TRIGGER_GI
+#define CRT_P_SHADE_TRIGGER_GI 28 // the GI continuation is long (sinf / cosf, basis, PCG): run it for nearly full warps only
+#endif
 #ifndef CRT_P_SHADE_TRIGGER
-#define CRT_P_SHADE_TRIGGER 20
+#define CRT_P_SHADE_TRIGGER 12
 #endif
 
 struct PersistCtl {
@@ -164,7 +173,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         if ((ply >= 0 || helper) && w.node != -1) { // fresh pixels have w.node == -1
             const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
 #pragma unroll
-            for (int k = 0; k < CRT_P_STEPS; ++k) {
+            for (int k = 0; k < (GI ? CRT_P_STEPS_GI : CRT_P_STEPS); ++k) {
                 if (w.node == -1 || blocked)
                     break;
                 bool need_pop = w.prune_at_visit(best_t);
@@ -250,7 +259,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         const unsigned ready_m = __ballot_sync(full, ready);
         const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && w.node != -1);
         patience = ready_m != 0u ? patience + 1 : 0;
-        if (ready_m != 0u && (__popc(ready_m) >= CRT_P_SHADE_TRIGGER || walking_m == 0u || patience >= CRT_P_PATIENCE)) {
+        if (ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u || patience >= (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE))) {
             patience = 0;
             if (ready) {
                 int act = 0; // 0: consume the finished query, 1: shade_ray(ray, depth) entry, 2: return c to the callers
