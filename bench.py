@@ -356,9 +356,9 @@ def run_ours(args):
             # the bound that actually binds (tree + triangles are L2 resident): issue slots = 148 SMs x 4 schedulers x f_SM
             slots = 148 * 4 * clocks["sm_mhz"] * 1e6 * (k_ms * 1e-3)
             issue = {"warp_instructions": prof["warp_instructions_per_frame"], "issue_slots": slots, "frac": prof["warp_instructions_per_frame"] / slots,
-                     "source": "smsp__inst_executed.sum of the trace launches in " + prof.get("source", "profiles/") + "; slots from the live kernel time and SM clock"}
+                     "source": "smsp__inst_executed.sum of the two walk kernels in " + prof.get("source", "profiles/") + "; slots from the live kernel time and SM clock"}
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "kernel": "k_wf_trace_light (all bounce levels of one frame; raygen/shade/resolve are < 5 % of the frame)", "kernel_ms": k_ms, "peak_source": peak_src,
+                "kernel": "closest-hit walk of one frame: k_wf_trace_light (primary level) + k_render_persistent<seeded> (every deeper level, shading included); raygen / level-0 shade / resolve are < 8 % of the frame", "kernel_ms": k_ms, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes,
                 "issue": issue,
                 "per_ray": {"kd_nodes_visited": counted["node_tests"] / max(1, counted["rays"]), "triangle_tests": counted["tri_tests"] / max(1, counted["rays"])}}
