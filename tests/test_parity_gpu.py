@@ -238,3 +238,28 @@ def test_persistent_pipeline_equals_the_other_pipelines_bit_for_bit(crt, ot, ren
     part, _, _ = renderer.render(crt.default_params(pipeline=crt.PIPELINE_PERSISTENT, rank=1, world=3, band_rows=5))
     rows = crt.Renderer.owned_rows(pers.shape[0], 1, 3, 5)
     assert same_bits(part, pers[rows])
+
+
+@pytest.mark.parametrize("rel", ["15-01-conclusion/scene1.crtscene", "11-01-refractive/scene8.crtscene"])
+def test_reference_walk_tree_and_heavy_leaf_kernel(crt, ot, renderer, rel, monkeypatch):
+    """CRT_WALK_TREE=reference (the reference tree with non-paying splits merged) is walked by k_wf_trace, the kernel
+    for heavy leaves (candidate ring + mailbox); either tree with either kernel gives the frame of the default setup."""
+    scene, flat = load(crt, ot, rel)
+    renderer.upload(flat)
+    want, want8, _ = renderer.render(crt.default_params())
+    for tree, kernel in (("reference", ""), ("reference", "light"), ("", "heavy")):
+        monkeypatch.setenv("CRT_WALK_TREE", tree)
+        monkeypatch.setenv("CRT_TRACE_KERNEL", kernel)
+        other = crt.Scene.load_json(ot.scene_variant(rel, *DEFAULT_SIZE), os.path.dirname(ot.scene_file(rel))).flatten()
+        assert (other.n_fast_nodes != flat.n_fast_nodes) == (tree == "reference")
+        r = crt.Renderer(0)
+        try:
+            r.upload(other)
+            for pipeline in (crt.PIPELINE_WAVEFRONT, crt.PIPELINE_MEGAKERNEL):
+                rgb, rgb8, _ = r.render(crt.default_params(pipeline=pipeline))
+                assert ppm_ok_fraction(rgb8, want8) >= 0.999
+                assert (otools.bits(rgb) == otools.bits(want)).all(axis=2).mean() >= 0.9999
+        finally:
+            r.close()
+    monkeypatch.delenv("CRT_WALK_TREE")
+    monkeypatch.delenv("CRT_TRACE_KERNEL")
