@@ -8,7 +8,7 @@
 // 18 % of the rays and take 55 % of the frame) and cannot run GI at all; the per-pixel megakernel can, but its lanes
 // sit in unrelated phases of trace / shade code (300 Mrays/s on the GI scene).  Here a warp alternates between three
 // phases, each entered only when enough lanes want it:
-//   WALK   every lane with an unfinished query visits up to CRT_L_STEPS nodes;
+//   WALK   every lane with an unfinished query visits up to CRT_P_STEPS nodes (CRT_P_STEPS_GI with GI);
 //   TEST   parked leaves of all lanes, one (ray, triangle) pair per lane and iteration;
 //   SHADE  lanes whose query is finished run the continuation of their pixel's recursion: shade the hit, then either
 //          start the next query (reflection, refraction, GI child, sibling) or finish the pixel and take a new one.
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                                                                                     PersistCtl *__restrict__ ctl, int patches_x, int n_slots_arg,
                                                                                     float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
                                                                                     Counters *__restrict__ counters, const __grid_constant__ WfBuffers b) {
-    const int n_slots = SEEDED ? b.ctl->count[1] : n_slots_arg;
+    const int n_slots = SEEDED ? level_count(b.ctl, b.cap, 1, 0) : n_slots_arg;
     const int base_depth = SEEDED ? 1 : 0;
     Counters cn{};
     __shared__ LightWarpShared shared[kTraceWarps];
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                 __syncwarp();
             }
         }
-        // ---- walk: up to CRT_L_STEPS node visits per lane; a leaf is parked and the walk goes on (speculatively: the
+        // ---- walk: a few node visits per lane; a leaf is parked and the walk goes on (speculatively: the
         //      leaf's triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong)
         bool blocked = false;
         if ((ply >= 0 || helper) && w.node != -1) { // fresh pixels have w.node == -1
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                             blocked = true; // both slots taken: wait for the test phase below
                         }
                     } else {
-                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn, S.kd_nodes);
+                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn);
                         need_pop = w.node < 0;
                     }
                 }

@@ -69,7 +69,6 @@ struct __align__(16) TraceWarpShared {
 // shared memory ([entry][lane]: conflict-free), older ones are spilled to local memory and rarely read back.
 constexpr uint32_t kFlagBit = 0x80000000u; // entry pushed for a ray lying IN the split plane: its interval starts at 0
 
-constexpr int kPopAgain = -2;
 constexpr int kStolenNode = 0x7FFFFFFF; // stack entry whose subtree a helper lane has taken over
 
 struct TraceWalker {
@@ -189,37 +188,6 @@ struct TraceWalker {
         return pruned | taken;
     }
 
-    // ONE pop attempt, straight-line (the light-leaf kernel calls it once per step slot instead of looping): node =
-    // the next subtree, -1 = the walk is over, kPopAgain = that entry was pruned, try the next one
-    template <bool STATS, class WS>
-    __device__ __forceinline__ void pop_once(WS &ws, uint2 *spill, unsigned lane, float best_t, Counters &cn) {
-        if (sp == 0) {
-            node = -1;
-            return;
-        }
-        --sp;
-        uint2 e = ws.stack[sp & (kWin - 1)][lane];
-        float below = __uint_as_float(ws.stack[(sp - 1) & (kWin - 1)][lane].y);
-        if (sp <= lo) { // rare: the entry or the one below it was spilled
-            if (sp < lo)
-                e = spill[sp], lo = sp;
-            if (sp > 0)
-                below = __uint_as_float(entry_at(ws, spill, lane, sp - 1).y);
-        }
-        tmax = sp == 0 ? root_tmax : below;
-        const bool flag = (e.x & kFlagBit) != 0u;
-        flagged -= flag ? 1 : 0;
-        tmin = flag ? 0.0f : __uint_as_float(e.y);
-        const bool pruned = !flag & (tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best_t);
-        node = pruned ? kPopAgain : int(e.x & ~kFlagBit);
-        if (node == kStolenNode) // the subtree was handed to a helper lane (k_wf_trace_light)
-            node = kPopAgain;
-        if (pruned & (flagged == 0) & (tmin - (fabsf(tmin) * 1e-3f + 1e-4f) > best_t)) // see pop(): everything below is pruned too
-            sp = 0, lo = 0, node = -1;
-        if (STATS && !pruned)
-            ++cn.node_tests;
-    }
-
     // ONE node of the walk: true when `n` is a leaf.  Same decisions as KdWalker::step, written as selects so that
     // the lanes of a warp, which sit at unrelated nodes, share one instruction stream; only the push and the pop stay
     // conditional.
@@ -230,7 +198,7 @@ struct TraceWalker {
 
     // `src` = the lane whose ray this walk belongs to (a helper lane walks a subtree of another lane's ray)
     template <bool STATS, class WS>
-    __device__ __forceinline__ bool step(WS &ws, uint2 *spill, unsigned lane, unsigned src, const int4 n, float best_t, Counters &cn, const int4 *prefetch = nullptr) {
+    __device__ __forceinline__ bool step(WS &ws, uint2 *spill, unsigned lane, unsigned src, const int4 n, float best_t, Counters &cn) {
         if (n.w == 3)
             return true;
         const int axis = n.w;
@@ -249,10 +217,6 @@ struct TraceWalker {
         const bool go_far = far_only | (both & !has_near);
         const int next = go_far ? far : near;
         push_if(ws, spill, lane, do_push, uint32_t(far) | (in_plane ? kFlagBit : 0u), in_plane ? tmax : tp);
-#ifdef CRT_PREFETCH_FAR
-        if (prefetch && do_push) // the far child is loaded many steps from now: have it in L2 by then
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(prefetch + far));
-#endif
         flagged += (do_push & in_plane) ? 1 : 0;
         tmax = (do_push & !in_plane) ? fminf(tmax, tp) : tmax;
         tmin = (both & !has_near & has_far & !in_plane) ? fmaxf(tmin, tp) : tmin;
@@ -335,8 +299,8 @@ template <int TRAV, bool STATS>
 __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
                                                           const __grid_constant__ WfBuffers b, int level, Counters *__restrict__ counters) {
     WfCtl *ctl = b.ctl;
-    const int total = level == 0 ? (TRAV == CRT_TRAVERSAL_KD ? ctl->count[0] : b.P) : ctl->count[level];
     const int start = level == 0 ? 0 : level_start(ctl, level);
+    const int total = level == 0 ? (TRAV == CRT_TRAVERSAL_KD ? ctl->count[0] : b.P) : level_count(ctl, b.cap, level, start);
     Counters cn{};
     if (TRAV != CRT_TRAVERSAL_KD) {
         trace_level_literal<STATS>(S, P, b, level, total, start, cn);

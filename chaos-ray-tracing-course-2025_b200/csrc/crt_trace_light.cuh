@@ -11,7 +11,10 @@
 //     test phase: shfl prefix sum of the parked triangle counts, owner lane by binary search, every lane tests
 //     whichever (ray, triangle) pair comes next.  After a phase every parked leaf of every lane has been tested, so a
 //     ray retires as soon as its walk is over and its slots are empty: no marks, no ring, no mailbox (a triangle
-//     referenced from two leaves is simply tested twice; the winner rule min (t, parse index) does not care).
+//     referenced from two leaves is simply tested twice; the winner rule min (t, parse index) does not care);
+//   * the pop is bare (TraceWalker::pop_fast): whether a popped subtree can still hold a closer hit is decided when
+//     it is visited (prune_at_visit), in the instruction stream all lanes share;
+//   * when the level's queue is empty, idle lanes take over the bottom stack entries of lanes that still walk.
 #pragma once
 
 namespace crtdev {
@@ -44,8 +47,8 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                                                                                  const __grid_constant__ WfBuffers b, int level,
                                                                                  Counters *__restrict__ counters) {
     WfCtl *ctl = b.ctl;
-    const int total = ctl->count[level];
     const int start = level == 0 ? 0 : level_start(ctl, level);
+    const int total = level == 0 ? ctl->count[0] : level_count(ctl, b.cap, level, start);
     Counters cn{};
     __shared__ LightWarpShared shared[kTraceWarps];
     LightWarpShared &ws = shared[threadIdx.x >> 5];
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                             blocked = true; // both slots taken: wait for the test phase below
                         }
                     } else {
-                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn, S.kd_nodes);
+                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn);
                         need_pop = w.node < 0;
                     }
                 }

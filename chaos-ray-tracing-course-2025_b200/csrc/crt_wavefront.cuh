@@ -54,6 +54,12 @@ struct WavefrontState {
 
 enum NodeKind : int { kTerminal = 0, kNodeReflect = 1, kNodeRefract = 2, kNodeTir = 3 };
 
+// rays of a level (level >= 1) that really have a record: a level that outgrew the pool (ctl->overflow; the host
+// discards the frame and renders it again with a larger pool) counted more rays than fit -- never read past the pool
+__device__ __forceinline__ int level_count(const WfCtl *ctl, int cap, int level, int start) {
+    return max(0, min(ctl->count[level], cap - start));
+}
+
 __device__ __forceinline__ int level_start(const WfCtl *ctl, int level) { // q-offset of a level (level >= 1)
     int s = 0;
     for (int l = 1; l < level; ++l)
@@ -144,8 +150,8 @@ constexpr int kShadeBlock = 128;
 __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
                                                           const __grid_constant__ WfBuffers b, int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
     WfCtl *ctl = b.ctl;
-    const int total = level == 0 ? b.P : ctl->count[level];
     const int start = level == 0 ? 0 : level_start(ctl, level);
+    const int total = level == 0 ? b.P : level_count(ctl, b.cap, level, start);
     const int next_start = level == 0 ? 0 : start + total;
     const unsigned lane = threadIdx.x & 31u;
     const V3 zero = mk(0.0f, 0.0f, 0.0f);
@@ -285,7 +291,7 @@ __global__ void __launch_bounds__(256) k_wf_resolve(const __grid_constant__ DSce
         }
         return;
     }
-    const int total = ctl->count[level], start = level_start(ctl, level);
+    const int start = level_start(ctl, level), total = level_count(ctl, b.cap, level, start);
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x) {
         const int node_id = b.P + start + k;
         const int4 rec = b.rec[node_id];
