@@ -31,6 +31,8 @@ EXPORTED_SYMBOLS = [
     "crt_cuda_render", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
     "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
     "crt_cuda_frame_create", "crt_cuda_frame_open", "crt_cuda_frame_attach", "crt_cuda_frame_pointer", "crt_cuda_push_bands",
+    "crt_cuda_group_create", "crt_cuda_group_destroy", "crt_cuda_group_last_error", "crt_cuda_group_size", "crt_cuda_group_upload_scene",
+    "crt_cuda_group_set_camera", "crt_cuda_group_render", "crt_cuda_group_frame", "crt_cuda_group_encode_ppm",
 ]
 
 
@@ -134,6 +136,15 @@ def _load_library():
         "crt_cuda_frame_attach": (C.c_int, [vp, vp, C.c_int, C.c_int]),
         "crt_cuda_frame_pointer": (C.c_int, [vp, P(vp), P(C.c_int), P(C.c_int)]),
         "crt_cuda_push_bands": (C.c_int, [vp]),
+        "crt_cuda_group_create": (C.c_int, [P(C.c_int), C.c_int, P(vp)]),
+        "crt_cuda_group_destroy": (None, [vp]),
+        "crt_cuda_group_last_error": (C.c_char_p, [vp]),
+        "crt_cuda_group_size": (C.c_int, [vp]),
+        "crt_cuda_group_upload_scene": (C.c_int, [vp, P(FlatScene)]),
+        "crt_cuda_group_set_camera": (C.c_int, [vp, P(Camera)]),
+        "crt_cuda_group_render": (C.c_int, [vp, P(RenderParams), vp, vp, P(RenderStats)]),
+        "crt_cuda_group_frame": (C.c_int, [vp, P(vp), P(C.c_int), P(C.c_int)]),
+        "crt_cuda_group_encode_ppm": (C.c_int, [vp, vp, C.c_size_t, P(C.c_size_t)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -336,6 +347,55 @@ class Renderer:
         if self._ctx:
             lib.crt_cuda_destroy(self._ctx)
             self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class RendererGroup:
+    """One host thread, several GPUs (crt_cuda_group_*): a context per device, scene replicated, the frame cut into
+    interleaved row bands that every device pushes into the frame on devices[0]."""
+
+    def __init__(self, devices):
+        self._g = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        rc = lib.crt_cuda_group_create(arr, len(devices), C.byref(self._g))
+        if rc != CRT_OK:
+            raise CrtError(f"crt_cuda_group_create failed ({rc}); the render path needs CUDA devices with peer access, there is no CPU fallback")
+        self.width = self.height = 0
+
+    def _check(self, rc, what):
+        if rc != CRT_OK:
+            raise CrtError(f"{what} failed ({rc}): {lib.crt_cuda_group_last_error(self._g).decode()}")
+
+    def upload(self, scene):
+        flat = scene.flatten() if isinstance(scene, Scene) else scene
+        self._check(lib.crt_cuda_group_upload_scene(self._g, C.byref(flat)), "crt_cuda_group_upload_scene")
+        self.width, self.height = flat.camera.width, flat.camera.height
+        return flat
+
+    def render(self, params: RenderParams | None = None, want_rgb=True, want_rgb8=True):
+        params = params or default_params()
+        rgb = np.empty((self.height, self.width, 3), np.float32) if want_rgb else None
+        rgb8 = np.empty((self.height, self.width, 3), np.uint8) if want_rgb8 else None
+        stats = RenderStats()
+        self._check(lib.crt_cuda_group_render(self._g, C.byref(params), _ptr(rgb), _ptr(rgb8), C.byref(stats)), "crt_cuda_group_render")
+        return rgb, rgb8, stats.as_dict()
+
+    def encode_ppm(self) -> bytes:
+        length = C.c_size_t()
+        self._check(lib.crt_cuda_group_encode_ppm(self._g, None, 0, C.byref(length)), "crt_cuda_group_encode_ppm")
+        buf = C.create_string_buffer(length.value)
+        self._check(lib.crt_cuda_group_encode_ppm(self._g, buf, length.value, C.byref(length)), "crt_cuda_group_encode_ppm")
+        return buf.raw[: length.value]
+
+    def close(self):
+        if self._g:
+            lib.crt_cuda_group_destroy(self._g)
+            self._g = None
 
     def __del__(self):
         try:

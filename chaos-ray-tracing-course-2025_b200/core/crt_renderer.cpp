@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 #include "../../include/crt_cuda.h"
 #include "crt_flatten.h"
@@ -15,8 +16,12 @@ namespace crt {
 
 struct DeviceScene {
     FlatScene flat;
-    crt_cuda_ctx *ctx{ nullptr };
-    ~DeviceScene() { crt_cuda_destroy(ctx); }
+    crt_cuda_ctx *ctx{ nullptr };     // one GPU ($CRT_DEVICE)
+    crt_cuda_group *group{ nullptr }; // several GPUs ($CRT_DEVICES=0,1,...): row bands, frame assembled on the first
+    ~DeviceScene() {
+        crt_cuda_destroy(ctx);
+        crt_cuda_group_destroy(group);
+    }
 };
 
 namespace {
@@ -28,10 +33,35 @@ int env_int(const char *name, int fallback) {
     return v && *v ? std::atoi(v) : fallback;
 }
 
+std::vector<int> env_devices() {
+    std::vector<int> out;
+    const char *v = std::getenv("CRT_DEVICES");
+    for (const char *p = v; p && *p;) {
+        char *end = nullptr;
+        const long d = std::strtol(p, &end, 10);
+        if (end == p)
+            break;
+        out.push_back(int(d));
+        p = *end == ',' ? end + 1 : end;
+    }
+    return out;
+}
+
 DeviceScene &device_scene(const Scene &scene) {
     if (scene.device)
         return *scene.device;
     auto dev = std::make_shared<DeviceScene>();
+    if (const std::vector<int> devices = env_devices(); devices.size() > 1) {
+        const int rc = crt_cuda_group_create(devices.data(), int(devices.size()), &dev->group);
+        if (rc != CRT_OK)
+            throw std::runtime_error("crt::render_image: cannot create CUDA contexts with peer access for $CRT_DEVICES (code " + std::to_string(rc) +
+                                     "); this build renders on the GPU only");
+        flatten_scene(scene, dev->flat);
+        if (crt_cuda_group_upload_scene(dev->group, &dev->flat.view) != CRT_OK)
+            throw std::runtime_error(std::string("crt::render_image: scene upload failed: ") + crt_cuda_group_last_error(dev->group));
+        scene.device = std::move(dev);
+        return *scene.device;
+    }
     const int rc = crt_cuda_create(env_int("CRT_DEVICE", 0), &dev->ctx);
     if (rc != CRT_OK)
         throw std::runtime_error("crt::render_image: cannot create a CUDA context (code " + std::to_string(rc) +
@@ -53,11 +83,12 @@ bool write_ppm_device(const Scene &scene, std::ostream &os) {
     if (!scene.device)
         return false;
     crt_cuda_ctx *ctx = scene.device->ctx;
+    crt_cuda_group *group = scene.device->group;
     size_t length = 0;
-    if (crt_cuda_encode_ppm(ctx, nullptr, 0, &length) != CRT_OK)
+    if ((group ? crt_cuda_group_encode_ppm(group, nullptr, 0, &length) : crt_cuda_encode_ppm(ctx, nullptr, 0, &length)) != CRT_OK)
         return false;
     std::string text(length, '\0');
-    if (crt_cuda_encode_ppm(ctx, text.data(), text.size(), &length) != CRT_OK)
+    if ((group ? crt_cuda_group_encode_ppm(group, text.data(), text.size(), &length) : crt_cuda_encode_ppm(ctx, text.data(), text.size(), &length)) != CRT_OK)
         return false;
     os.write(text.data(), std::streamsize(length));
     return true;
@@ -87,8 +118,14 @@ Image render_image(const Scene &scene, const RendererSettings &settings) {
     // the camera may have been moved since the upload (Camera::pan_around & co.): resend the 72 B block
     const crt_camera cam = flatten_camera(scene.camera);
     crt_render_stats stats{};
-    if (crt_cuda_set_camera(dev.ctx, &cam) != CRT_OK ||
-        crt_cuda_render(dev.ctx, &params, reinterpret_cast<float *>(result.buffer.data()), nullptr, &stats) != CRT_OK)
+    if (dev.group) {
+        // the quantised frame is assembled on the first device as well, so that write_ppm_device can format it there
+        std::vector<uint8_t> rgb8(size_t(result.width) * size_t(result.height) * 3);
+        if (crt_cuda_group_set_camera(dev.group, &cam) != CRT_OK ||
+            crt_cuda_group_render(dev.group, &params, reinterpret_cast<float *>(result.buffer.data()), rgb8.data(), &stats) != CRT_OK)
+            throw std::runtime_error(std::string("crt::render_image: ") + crt_cuda_group_last_error(dev.group));
+    } else if (crt_cuda_set_camera(dev.ctx, &cam) != CRT_OK ||
+               crt_cuda_render(dev.ctx, &params, reinterpret_cast<float *>(result.buffer.data()), nullptr, &stats) != CRT_OK)
         throw std::runtime_error(std::string("crt::render_image: ") + crt_cuda_last_error(dev.ctx));
 
     const auto t2 = clock::now();

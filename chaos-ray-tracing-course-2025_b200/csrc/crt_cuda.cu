@@ -32,6 +32,7 @@ struct crt_cuda_ctx {
     bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
     crt_render_params last_params{};
     bool last_wavefront = false;
+    bool rerendered = false; // crt_cuda_synchronize had to render the frame again (a bounce level outgrew the ray pool)
 
     float *d_rgb = nullptr;
     uint8_t *d_rgb8 = nullptr;
@@ -485,7 +486,9 @@ int crt_cuda_synchronize(crt_cuda_ctx *ctx, crt_render_stats *stats) {
     CRT_CK(ctx, cudaSetDevice(ctx->device));
     CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
     // a bounce level outgrew the ray pool: grow it and render the frame again (rare; the pool then stays large)
+    ctx->rerendered = false;
     for (int attempt = 0; ctx->last_wavefront && ctx->wf.h_flags && *ctx->wf.h_flags && attempt < 6; ++attempt) {
+        ctx->rerendered = true;
         *ctx->wf.h_flags = 0;
         ctx->wf.grow *= 2.0;
         const crt_render_params again = ctx->last_params;
@@ -674,6 +677,187 @@ int crt_cuda_push_bands(crt_cuda_ctx *ctx) {
         k_push_bands<uint8_t><<<blocks, 256, 0, ctx->stream>>>(ctx->d_rgb8, ctx->frame, dp.rows, int(units), dp);
     CRT_CK(ctx, cudaGetLastError());
     return CRT_OK;
+}
+
+// ---- one host thread driving several GPUs (crt_cuda_group_*): a context per device, the scene
+// replicated, the frame cut into interleaved row bands, every device pushing its bands into the frame on devices[0]
+struct crt_cuda_group {
+    std::vector<crt_cuda_ctx *> ranks;
+    std::string error;
+};
+
+int crt_cuda_group_create(const int *devices, int n, crt_cuda_group **out) {
+    if (!out)
+        return CRT_ERR_INVALID;
+    *out = nullptr;
+    if (!devices || n < 1)
+        return CRT_ERR_INVALID;
+    crt_cuda_group *g = new crt_cuda_group;
+    for (int i = 0; i < n; ++i) {
+        crt_cuda_ctx *ctx = nullptr;
+        const int rc = crt_cuda_create(devices[i], &ctx);
+        if (rc != CRT_OK) {
+            crt_cuda_group_destroy(g);
+            return rc;
+        }
+        g->ranks.push_back(ctx);
+    }
+    // peer stores into devices[0]'s frame need peer access from every other device (same-device contexts need nothing)
+    for (int i = 1; i < n; ++i) {
+        if (devices[i] == devices[0])
+            continue;
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, devices[i], devices[0]);
+        if (!can) {
+            crt_cuda_group_destroy(g);
+            return CRT_ERR_CUDA;
+        }
+        cudaSetDevice(devices[i]);
+        const cudaError_t e = cudaDeviceEnablePeerAccess(devices[0], 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+            crt_cuda_group_destroy(g);
+            return CRT_ERR_CUDA;
+        }
+        cudaGetLastError();
+    }
+    *out = g;
+    return CRT_OK;
+}
+
+void crt_cuda_group_destroy(crt_cuda_group *g) {
+    if (!g)
+        return;
+    for (size_t i = g->ranks.size(); i-- > 0;) // rank 0 owns the frame the others point into: release it last
+        crt_cuda_destroy(g->ranks[i]);
+    delete g;
+}
+
+const char *crt_cuda_group_last_error(const crt_cuda_group *g) { return g ? g->error.c_str() : "null group"; }
+
+int crt_cuda_group_size(const crt_cuda_group *g) { return g ? int(g->ranks.size()) : 0; }
+
+int crt_cuda_group_upload_scene(crt_cuda_group *g, const crt_flat_scene *scene) {
+    if (!g)
+        return CRT_ERR_INVALID;
+    for (crt_cuda_ctx *ctx : g->ranks)
+        if (int rc = crt_cuda_upload_scene(ctx, scene)) {
+            g->error = ctx->error;
+            return rc;
+        }
+    return CRT_OK;
+}
+
+int crt_cuda_group_set_camera(crt_cuda_group *g, const crt_camera *camera) {
+    if (!g)
+        return CRT_ERR_INVALID;
+    for (crt_cuda_ctx *ctx : g->ranks)
+        if (int rc = crt_cuda_set_camera(ctx, camera)) {
+            g->error = ctx->error;
+            return rc;
+        }
+    return CRT_OK;
+}
+
+int crt_cuda_group_render(crt_cuda_group *g, const crt_render_params *params, float *rgb_out, uint8_t *rgb8_out, crt_render_stats *stats) {
+    if (!g || !params)
+        return CRT_ERR_INVALID;
+    const int n = int(g->ranks.size());
+    crt_cuda_ctx *root = g->ranks[0];
+    if (!root->have_scene) {
+        g->error = "no scene uploaded";
+        return CRT_ERR_INVALID;
+    }
+    const int W = root->scene.cam.width, H = root->scene.cam.height;
+#define CRT_GROUP_CK(ctx, call)            \
+    if (int rc_ = (call)) {                \
+        g->error = (ctx)->error;           \
+        return rc_;                        \
+    }
+    if (W > 0 && H > 0 && (root->frame_kind != 1 || root->frame_w != W || root->frame_h != H)) {
+        CRT_GROUP_CK(root, crt_cuda_frame_create(root, W, H, nullptr));
+        for (int i = 1; i < n; ++i)
+            CRT_GROUP_CK(g->ranks[i], crt_cuda_frame_attach(g->ranks[i], root->frame, W, H));
+    }
+    const int band = params->band_rows > 0 ? params->band_rows : 8;
+    // a device's outputs: its bands into the frame on devices[0] (peer stores) and / or its float rows straight to their
+    // place in the caller's frame, band by band
+    auto issue_outputs = [&](crt_cuda_ctx *ctx, int i) -> int {
+        if (W <= 0 || H <= 0 || ctx->last_rows <= 0)
+            return CRT_OK;
+        if (rgb8_out)
+            if (int rc = crt_cuda_push_bands(ctx))
+                return rc;
+        if (rgb_out) {
+            const size_t row_bytes = size_t(W) * 3 * sizeof(float);
+            int local = 0;
+            for (int b = i; b * band < H; b += n) {
+                const int rows = std::min(band, H - b * band);
+                const cudaError_t e = cudaMemcpyAsync(reinterpret_cast<char *>(rgb_out) + size_t(b) * band * row_bytes,
+                                                      reinterpret_cast<const char *>(ctx->d_rgb) + size_t(local) * row_bytes, size_t(rows) * row_bytes,
+                                                      cudaMemcpyDeviceToHost, ctx->stream);
+                if (e != cudaSuccess) {
+                    ctx->error = cudaGetErrorString(e);
+                    return CRT_ERR_CUDA;
+                }
+                local += rows;
+            }
+        }
+        return CRT_OK;
+    };
+    // enqueue everything on every device first (the devices then work concurrently), complete afterwards
+    for (int i = 0; i < n; ++i) {
+        crt_cuda_ctx *ctx = g->ranks[i];
+        crt_render_params p = *params;
+        p.rank = i, p.world = n, p.band_rows = band;
+        CRT_GROUP_CK(ctx, enqueue_frame(ctx, &p));
+        CRT_GROUP_CK(ctx, issue_outputs(ctx, i));
+    }
+    crt_render_stats total{};
+    for (int i = 0; i < n; ++i) {
+        crt_render_stats st{};
+        CRT_GROUP_CK(g->ranks[i], crt_cuda_synchronize(g->ranks[i], &st));
+        if (g->ranks[i]->rerendered) { // the frame was rendered again with a larger ray pool: its outputs once more
+            CRT_GROUP_CK(g->ranks[i], issue_outputs(g->ranks[i], i));
+            if (cudaStreamSynchronize(g->ranks[i]->stream) != cudaSuccess) {
+                g->error = "cudaStreamSynchronize failed";
+                return CRT_ERR_CUDA;
+            }
+        }
+        total.gpu_ms = std::max(total.gpu_ms, st.gpu_ms);
+        total.kernel_launches += st.kernel_launches;
+        total.rows_rendered += st.rows_rendered;
+        total.rays += st.rays, total.shadow_rays += st.shadow_rays, total.node_tests += st.node_tests, total.tri_tests += st.tri_tests;
+        for (int k = 0; k < 16; ++k)
+            total.rays_by_depth[k] += st.rays_by_depth[k];
+    }
+    if (rgb8_out && W > 0 && H > 0) { // every device's push has completed: one copy of the assembled frame
+        cudaSetDevice(root->device);
+        const cudaError_t e = cudaMemcpy(rgb8_out, root->frame, size_t(W) * size_t(H) * 3, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            g->error = cudaGetErrorString(e);
+            return CRT_ERR_CUDA;
+        }
+    }
+#undef CRT_GROUP_CK
+    if (stats)
+        *stats = total;
+    return CRT_OK;
+}
+
+int crt_cuda_group_encode_ppm(crt_cuda_group *g, char *text_out, size_t capacity, size_t *length) {
+    if (!g)
+        return CRT_ERR_INVALID;
+    crt_cuda_ctx *root = g->ranks[0];
+    const int rc = crt_cuda_encode_ppm_device(root, root->frame, root->frame_w, root->frame_h, text_out, capacity, length);
+    if (rc)
+        g->error = root->error;
+    return rc;
+}
+
+int crt_cuda_group_frame(crt_cuda_group *g, void **frame_dev, int *width, int *height) {
+    if (!g)
+        return CRT_ERR_INVALID;
+    return crt_cuda_frame_pointer(g->ranks[0], frame_dev, width, height);
 }
 
 int crt_cuda_encode_ppm_device(crt_cuda_ctx *ctx, const void *rgb8_dev, int width, int height, char *text_out, size_t capacity, size_t *length) {

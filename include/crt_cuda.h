@@ -227,6 +227,24 @@ int crt_cuda_frame_attach(crt_cuda_ctx *ctx, void *frame_dev, int width, int hei
 int crt_cuda_frame_pointer(crt_cuda_ctx *ctx, void **frame_dev, int *width, int *height);
 int crt_cuda_push_bands(crt_cuda_ctx *ctx);
 
+/* One host thread, several GPUs of one box: a context per device, scene replicated, one frame cut into interleaved
+ * row bands (band b -> devices[b % n]), every device pushing its bands into the frame on devices[0] (peer access).
+ * group_render fills HOST buffers like crt_cuda_render: rgb_out = width*height*3 floats, rgb8_out = width*height*3
+ * bytes (either may be NULL); params->rank/world are set by the group.  stats: gpu_ms = slowest device, counters summed.
+ * The same device may be listed more than once (contexts share it; used by the tests). */
+typedef struct crt_cuda_group crt_cuda_group;
+int crt_cuda_group_create(const int *devices, int n, crt_cuda_group **out);
+void crt_cuda_group_destroy(crt_cuda_group *group);
+const char *crt_cuda_group_last_error(const crt_cuda_group *group);
+int crt_cuda_group_size(const crt_cuda_group *group);
+int crt_cuda_group_upload_scene(crt_cuda_group *group, const crt_flat_scene *scene);
+int crt_cuda_group_set_camera(crt_cuda_group *group, const crt_camera *camera);
+int crt_cuda_group_render(crt_cuda_group *group, const crt_render_params *params, float *rgb_out, uint8_t *rgb8_out, crt_render_stats *stats);
+/* the assembled quantised frame on devices[0] (for crt_cuda_encode_ppm_device) */
+int crt_cuda_group_frame(crt_cuda_group *group, void **frame_dev, int *width, int *height);
+/* P3 text of that frame (needs a group_render with rgb8_out != NULL before) */
+int crt_cuda_group_encode_ppm(crt_cuda_group *group, char *text_out, size_t capacity, size_t *length);
+
 /* P3 text encoding of the last frame on the device (crt_image_ppm.cpp:9-23), byte-exact.
  * Returns the byte count in *length; text_out may be NULL to query the size. */
 int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size_t *length);

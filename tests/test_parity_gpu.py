@@ -263,3 +263,27 @@ def test_reference_walk_tree_and_heavy_leaf_kernel(crt, ot, renderer, rel, monke
             r.close()
     monkeypatch.delenv("CRT_WALK_TREE")
     monkeypatch.delenv("CRT_TRACE_KERNEL")
+
+
+@pytest.mark.parametrize("n_devices", [1, 2, 3])
+def test_device_group_renders_the_frame(crt, ot, renderer, n_devices):
+    """crt_cuda_group_* (one host thread, a context per device; here the same GPU listed several times, on a multi-GPU
+    box real peers): float frame and quantised frame equal the single-context render; PPM of the assembled frame."""
+    import torch
+    devices = [k % max(1, torch.cuda.device_count()) for k in range(n_devices)]
+    for rel, size in (("15-01-conclusion/scene1.crtscene", (322, 181)), ("11-01-refractive/scene8.crtscene", (320, 180)),
+                      ("15-01-conclusion/scene2.crtscene", (96, 96))):
+        scene, flat = load(crt, ot, rel, size)
+        renderer.upload(flat)
+        want, want8, st = renderer.render(crt.default_params(collect_stats=1))
+        group = crt.RendererGroup(devices)
+        try:
+            group.upload(flat)
+            rgb, rgb8, gst = group.render(crt.default_params(collect_stats=1, band_rows=5))
+            assert same_bits(rgb, want) and np.array_equal(rgb8, want8)
+            assert gst["rays"] == st["rays"] and gst["rows_rendered"] == size[1]
+            assert group.encode_ppm() == renderer.encode_ppm()
+            only8 = group.render(crt.default_params(), want_rgb=False)[1]
+            assert np.array_equal(only8, want8)
+        finally:
+            group.close()
