@@ -235,8 +235,13 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
                 return fail(ctx, CRT_ERR_INVALID, "the hybrid pipeline handles neither GI, shadow rays nor the literal traversal");
             int launches = 0;
             const bool deeper = ctx->has_secondary && dp.max_ray_depth > 0;
+            // levels 0 .. seed-1 as wavefront kernels; $CRT_HYBRID_LEVEL moves the hand-over
+            int seed = dp.max_ray_depth >= 5 && params->world <= 1 ? 2 : 1; // C4: 3.09 ms with 1, 3.01 ms with 2
+            if (const char *v = std::getenv("CRT_HYBRID_LEVEL"); v && *v)
+                seed = std::max(1, std::atoi(v));
+            seed = deeper ? std::min(seed, int(dp.max_ray_depth)) : 1;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
-                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, true);
+                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, seed);
             ctx->last_wavefront = true;
             if (e != cudaSuccess)
                 return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
@@ -244,9 +249,12 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
                 if (!ctx->d_pctl)
                     CRT_CK(ctx, cudaMalloc(&ctx->d_pctl, sizeof(PersistCtl)));
                 CRT_CK(ctx, cudaMemsetAsync(ctx->d_pctl, 0, sizeof(PersistCtl), ctx->stream));
-                launch_persistent<true>(ctx, dp, stats, false, ctx->wf.sm_count * CRT_P_MINBLOCKS, 0, 0);
-                k_wf_resolve<<<ctx->wf.sm_count * 4, 256, 0, ctx->stream>>>(ctx->scene, dp, ctx->wf.b, 0, ctx->d_rgb, ctx->d_rgb8);
-                launches += 2;
+                launch_persistent<true>(ctx, dp, stats, false, ctx->wf.sm_count * CRT_P_MINBLOCKS, seed, 0);
+                ++launches;
+                for (int level = seed - 1; level >= 0; --level) {
+                    k_wf_resolve<<<ctx->wf.sm_count * 4, 256, 0, ctx->stream>>>(ctx->scene, dp, ctx->wf.b, level, ctx->d_rgb, ctx->d_rgb8);
+                    ++launches;
+                }
             }
             ctx->last_launches = launches;
         } else if (pipeline == CRT_PIPELINE_WAVEFRONT) {

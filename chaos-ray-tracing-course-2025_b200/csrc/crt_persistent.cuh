@@ -62,8 +62,10 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                                                                                     PersistCtl *__restrict__ ctl, int patches_x, int n_slots_arg,
                                                                                     float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
                                                                                     Counters *__restrict__ counters, const __grid_constant__ WfBuffers b) {
-    const int n_slots = SEEDED ? level_count(b.ctl, b.cap, 1, 0) : n_slots_arg;
-    const int base_depth = SEEDED ? 1 : 0;
+    // SEEDED: `patches_x` carries the bounce level whose queued rays are the seeds (1 = everything below the primary level)
+    const int base_depth = SEEDED ? patches_x : 0;
+    const int seed_start = SEEDED ? level_start(b.ctl, base_depth) : 0;
+    const int n_slots = SEEDED ? level_count(b.ctl, b.cap, base_depth, seed_start) : n_slots_arg;
     Counters cn{};
     __shared__ LightWarpShared shared[kTraceWarps];
     LightWarpShared &ws = shared[threadIdx.x >> 5];
@@ -108,7 +110,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                 int x, ly;
                 if (slot < n_slots && (SEEDED || persist_slot_pixel(slot, patches_x, S.cam.width, P.rows, x, ly))) {
                     if (SEEDED)
-                        x = slot, ly = 0; // px = index of my level-1 ray
+                        x = slot, ly = 0; // px = index of my seed ray within its level
                     px = x, ply = ly, depth = base_depth;
                     fresh = true, live = false;
                     src = lane, stolen = 0;
@@ -268,7 +270,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                 if (fresh) {
                     fresh = false;
                     if (SEEDED) {
-                        ray = Ray{ xyz(b.ray_o[px]), xyz(b.ray_d[px]) };
+                        ray = Ray{ xyz(b.ray_o[seed_start + px]), xyz(b.ray_d[seed_start + px]) };
                     } else {
                         const int y = global_row(P, ply);
                         if (GI)
@@ -366,7 +368,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                     // act == 2: return c to the callers (the frame stack is the recursion's return path)
                     if (depth == base_depth) {
                         if (SEEDED)
-                            b.col[b.P + px] = make_float4(c.x, c.y, c.z, 0.0f);
+                            b.col[b.P + seed_start + px] = make_float4(c.x, c.y, c.z, 0.0f);
                         else
                             write_pixel(S, rgb, rgb8, px, ply, c);
                         ply = -1;

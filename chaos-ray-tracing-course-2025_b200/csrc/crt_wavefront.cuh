@@ -398,7 +398,7 @@ inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, con
 // `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_light instead of k_wf_trace
 inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
                                     uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves,
-                                    bool primary_level_only = false) {
+                                    int first_levels_only = 0) {
     const int patches_x = (S.cam.width + 7) / 8, patches_y = (dp.rows + 3) / 4;
     const int P = patches_x * patches_y * 32;
     secondary = secondary && dp.max_ray_depth > 0;
@@ -408,9 +408,10 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     w.b.patches_x = patches_x;
     if ((e = cudaMemsetAsync(w.b.ctl, 0, sizeof(WfCtl), stream)) != cudaSuccess)
         return e;
-    // primary_level_only (hybrid pipeline): raygen, trace and shade of level 0 only; the caller evaluates the queued
-    // level-1 rays' subtrees (k_render_persistent<SEEDED>) and then runs the level-0 resolve
-    const int levels = secondary && !primary_level_only ? int(dp.max_ray_depth) + 1 : 1;
+    // first_levels_only = L > 0 (hybrid pipeline): raygen, then trace and shade of levels 0 .. L-1 only; the caller
+    // evaluates the subtrees of the queued level-L rays (k_render_persistent<SEEDED>) and runs the resolves of levels L-1 .. 0
+    const int all_levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
+    const int levels = first_levels_only > 0 ? min(first_levels_only, all_levels) : all_levels;
     const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? CRT_L_MINBLOCKS : 8);
     int n = 0;
     if (traversal != CRT_TRAVERSAL_LITERAL) {
@@ -431,7 +432,7 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
         k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
         n += 2;
     }
-    for (int level = levels - 2; level >= 0; --level) {
+    for (int level = levels - 2; level >= 0 && first_levels_only <= 0; --level) {
         k_wf_resolve<<<w.sm_count * 4, 256, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
         ++n;
     }
