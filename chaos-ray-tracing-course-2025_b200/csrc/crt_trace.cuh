@@ -95,7 +95,7 @@ struct TraceWalker {
     template <class WS>
     __device__ __forceinline__ void push_if(WS &ws, uint2 *spill, unsigned lane, bool doit, uint32_t tagged_node, float entry) {
         const bool full = sp - lo == kWin;
-        if (doit & full) { // window full (rare): the oldest entry goes to local memory
+        if (__builtin_expect(doit & full, 0)) { // window full (rare): the oldest entry goes to local memory
             spill[lo] = ws.stack[lo & (kWin - 1)][lane];
             ++lo;
         }
@@ -155,25 +155,22 @@ struct TraceWalker {
     // instructions at 3.9 threads per instruction).
     template <bool STATS, class WS>
     __device__ __forceinline__ void pop_fast(WS &ws, uint2 *spill, unsigned lane, Counters &cn) {
-        if (sp == 0) {
-            node = -1;
-            return;
-        }
-        --sp;
+        const bool empty = sp == 0; // nothing pending: the walk is over (the loads below then read slot -1 & 7, unused)
+        sp -= empty ? 0 : 1;
         uint2 e = ws.stack[sp & (kWin - 1)][lane];
         float below = __uint_as_float(ws.stack[(sp - 1) & (kWin - 1)][lane].y);
-        if (sp <= lo) { // rare: the entry or the one below it was spilled
+        if (__builtin_expect(!empty & (sp <= lo), 0)) { // rare: the entry or the one below it was spilled
             if (sp < lo)
                 e = spill[sp], lo = sp;
             if (sp > 0)
                 below = __uint_as_float(entry_at(ws, spill, lane, sp - 1).y);
         }
         tmax = sp == 0 ? root_tmax : below;
-        const bool flag = (e.x & kFlagBit) != 0u;
+        const bool flag = !empty & ((e.x & kFlagBit) != 0u);
         flagged -= flag ? 1 : 0;
         tmin = flag ? 0.0f : __uint_as_float(e.y);
-        node = int(e.x & ~kFlagBit);
-        if (STATS)
+        node = empty ? -1 : int(e.x & ~kFlagBit);
+        if (STATS && !empty)
             ++cn.node_tests;
     }
 
@@ -203,8 +200,10 @@ struct TraceWalker {
             return true;
         const int axis = n.w;
         const float split = __int_as_float(n.x);
-        const float oa = ws.ray[axis][src], da = ws.ray[3 + axis][src], ia = ws.ray[6 + axis][src];
-        const bool below = (oa < split) | ((oa == split) & (da <= 0.0f));
+        // an origin exactly ON the plane takes the side the ray leaves towards; the sign of 1/d is the sign of d (d = +-0
+        // with the origin on the plane is the in-plane case below, where both sides are visited whatever `below` says)
+        const float oa = ws.ray[axis][src], ia = ws.ray[6 + axis][src];
+        const bool below = (oa < split) | ((oa == split) & (ia <= 0.0f));
         const int near = below ? n.y : n.z, far = below ? n.z : n.y;
         const float tp = (split - oa) * ia;
         const float slack = fabsf(tp) * 1e-5f + 1e-6f;
