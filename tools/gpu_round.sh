@@ -13,6 +13,6 @@ timeout 300 python tools/render_frames.py c3-gi 3 auto kd 1 2>&1 | tail -1 | tee
 [ "$2" = "skip-ncu" ] && exit 0
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches_c4.csv \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${tag}_ncu_launches.log 2>&1; echo "ncu launches exit $?"
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"k_wf_trace|k_render_persistent" -c 2 -f -o gpurun_out/${tag}_trace_c4 \
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"k_wf_trace|k_render_persistent" -c 3 -f -o gpurun_out/${tag}_trace_c4 \
   python tools/render_frames.py c4 1 auto kd 0 > gpurun_out/${tag}_ncu_full.log 2>&1; echo "ncu full exit $?"
 ls -la gpurun_out | tail -20
