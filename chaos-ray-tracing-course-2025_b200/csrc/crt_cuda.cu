@@ -151,10 +151,10 @@ void launch_mega(crt_cuda_ctx *ctx, const DParams &dp, bool stats, dim3 grid) {
         k_render_mega<TRAV, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters);
 }
 
-template <bool SEEDED>
+template <bool SEEDED, bool SHADOWS>
 void launch_persistent(crt_cuda_ctx *ctx, const DParams &dp, bool stats, bool gi, int blocks, int patches_x, int n_slots) {
 #define CRT_LAUNCH_P(ST, G) \
-    k_render_persistent<ST, G, SEEDED><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, ctx->wf.b)
+    k_render_persistent<ST, G, SEEDED, SHADOWS><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, ctx->wf.b)
     if (gi && stats)
         CRT_LAUNCH_P(true, true);
     else if (gi)
@@ -195,9 +195,10 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         int pipeline = params->pipeline;
         const bool needs_mega = (ctx->scene.gi_on && dp.gi_rays > 0) || params->shadows;
         if (pipeline == CRT_PIPELINE_AUTO)
-            // GI keeps a pixel's recursion on one lane (RNG order): the persistent kernel; shadow rays and the
-            // verification traversal: the per-pixel megakernel; everything else: the wavefront
-            pipeline = params->shadows || (needs_mega && params->traversal != CRT_TRAVERSAL_KD) ? CRT_PIPELINE_MEGAKERNEL
+            // GI keeps a pixel's recursion on one lane (RNG order), and so do the light loops of the flagged shadow mode
+            // (one shadow query per light): the persistent kernel; those under the verification traversal: the
+            // per-pixel megakernel; everything else: the wavefront
+            pipeline = needs_mega && params->traversal != CRT_TRAVERSAL_KD ? CRT_PIPELINE_MEGAKERNEL
                        : needs_mega                                                              ? CRT_PIPELINE_PERSISTENT
                                                                                                  : CRT_PIPELINE_WAVEFRONT;
             // deep recursions and band-sharded frames end in many small bounce levels, each lasting as long as its
@@ -207,8 +208,6 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
                 (dp.max_ray_depth >= 5 || params->world > 1))
                 pipeline = CRT_PIPELINE_HYBRID;
         if (pipeline == CRT_PIPELINE_PERSISTENT) {
-            if (params->shadows)
-                return fail(ctx, CRT_ERR_INVALID, "the persistent pipeline does not trace shadow rays; use CRT_PIPELINE_MEGAKERNEL");
             if (params->traversal != CRT_TRAVERSAL_KD)
                 return fail(ctx, CRT_ERR_INVALID, "the persistent pipeline walks the k-d walk tree only (CRT_TRAVERSAL_KD)");
             if (!ctx->d_pctl)
@@ -223,7 +222,10 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
             }
             const bool gi_frame = ctx->scene.gi_on && dp.gi_rays > 0;
             const int blocks = std::min(ctx->sm_count * (gi_frame ? CRT_P_MINBLOCKS_GI : CRT_P_MINBLOCKS), (n_slots + kTraceBlock - 1) / kTraceBlock);
-            launch_persistent<false>(ctx, dp, stats, gi_frame, blocks, patches_x, n_slots);
+            if (params->shadows)
+                launch_persistent<false, true>(ctx, dp, stats, gi_frame, blocks, patches_x, n_slots);
+            else
+                launch_persistent<false, false>(ctx, dp, stats, gi_frame, blocks, patches_x, n_slots);
             ctx->last_launches = 1;
         } else if (pipeline == CRT_PIPELINE_WAVEFRONT && needs_mega)
             return fail(ctx, CRT_ERR_INVALID, "the wavefront pipeline does not handle GI or shadow rays; use CRT_PIPELINE_MEGAKERNEL");
@@ -249,7 +251,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
                 if (!ctx->d_pctl)
                     CRT_CK(ctx, cudaMalloc(&ctx->d_pctl, sizeof(PersistCtl)));
                 CRT_CK(ctx, cudaMemsetAsync(ctx->d_pctl, 0, sizeof(PersistCtl), ctx->stream));
-                launch_persistent<true>(ctx, dp, stats, false, ctx->wf.sm_count * CRT_P_MINBLOCKS, seed, 0);
+                launch_persistent<true, false>(ctx, dp, stats, false, ctx->wf.sm_count * CRT_P_MINBLOCKS, seed, 0);
                 ++launches;
                 for (int level = seed - 1; level >= 0; --level) {
                     k_wf_resolve<<<ctx->wf.sm_count * 4, 256, 0, ctx->stream>>>(ctx->scene, dp, ctx->wf.b, level, ctx->d_rgb, ctx->d_rgb8);

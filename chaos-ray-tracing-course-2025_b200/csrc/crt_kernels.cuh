@@ -81,7 +81,8 @@ __global__ void __launch_bounds__(kBlock) k_primary_hits(const __grid_constant__
 // frame stack instead of recursion.  Evaluation order is the reference's: GI children in index order before the
 // light loop, reflection subtree before refraction subtree, one PCG32 stream per pixel consumed in that order --
 // so float results are combined in exactly the nesting the CPU uses.
-enum FrameKind : int { kDiffuseGi = 0, kReflect = 1, kRefractWaitReflection = 2, kRefractWaitRefraction = 3, kRefractTir = 4 };
+enum FrameKind : int { kDiffuseGi = 0, kReflect = 1, kRefractWaitReflection = 2, kRefractWaitRefraction = 3, kRefractTir = 4,
+                       kDirectShadow = 5 /* k_render_persistent: light loop with one shadow query per light */ };
 
 struct Frame {
     int kind, i;

@@ -53,11 +53,30 @@ __device__ __forceinline__ bool persist_slot_pixel(int slot, int patches_x, int 
     return x < width && ly < rows;
 }
 
+// one light of add_direct_light (crt_device.cuh), same operation sequence
+struct LightTerm {
+    V3 dir;
+    float r2, cos_law, area, intensity;
+};
+__device__ __forceinline__ LightTerm light_term(const DScene &S, int i, V3 Pnt, V3 n) {
+    const float four_pi = 4.0f * 3.14159274101257324219f;
+    const float4 L = __ldg(&S.lights[i]);
+    LightTerm t;
+    V3 dir = xyz(L) - Pnt;
+    t.r2 = dot(dir, dir);
+    t.dir = dir / sqrtf(t.r2);
+    const float ln = dot(t.dir, n);
+    t.cos_law = (0.0f < ln) ? ln : 0.0f;
+    t.area = four_pi * t.r2;
+    t.intensity = L.w;
+    return t;
+}
+
 // SEEDED: the work items are not pixels but the level-1 rays the wavefront's level-0 shade stage queued (hybrid
 // pipeline: the dense, coherent primary level runs as raygen / trace / shade kernels at full SIMD width, everything
 // deeper runs here).  A lane takes a level-1 ray, evaluates its whole subtree depth-first and stores the subtree's
 // colour in the level-1 node record, which the level-0 resolve kernel combines as before.
-template <bool STATS, bool GI, bool SEEDED>
+template <bool STATS, bool GI, bool SEEDED, bool SHADOWS>
 __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_MINBLOCKS) k_render_persistent(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
                                                                                     PersistCtl *__restrict__ ctl, int patches_x, int n_slots_arg,
                                                                                     float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
@@ -84,6 +103,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     int depth = 0;
     bool live = false;    // the current query entered the root box (its result is in ws.best[lane])
     bool fresh = false;   // pixel just taken: its primary ray has not been generated yet (done in the SHADE phase)
+    bool shadow_q = false; // the running query is a shadow ray of frames[depth]'s light loop, not a shade_ray call
     Pcg32 rng{};
     Frame frames[kMaxDepthCap + 1];
     // ---- walk state (see k_wf_trace_light)
@@ -304,6 +324,24 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                         act = 0;
                         continue;
                     }
+                    if (act == 3) { // shadow query of the light loop (flagged mode, crt_renderer.cpp:88-92 as intended)
+                        if (STATS) {
+                            ++cn.shadow_rays;
+                            ++cn.node_tests;
+                        }
+                        shadow_q = true;
+                        const RaySetup q = ray_setup(S, ray);
+                        if (q.live) {
+                            w.start(ws, lane, ray.o, ray.d, q.inv, q.tmin, q.tmax);
+                            ws.best[lane] = kNoHitKey;
+                            live = true;
+                            stolen = 0;
+                            break;
+                        }
+                        live = false;
+                        act = 0;
+                        continue;
+                    }
                     if (act == 0) {
                         Hit h{ kInf, -1 };
                         if (live) {
@@ -313,6 +351,22 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                             ray = Ray{ mk(ws.ray[0][lane], ws.ray[1][lane], ws.ray[2][lane]), mk(ws.ray[3][lane], ws.ray[4][lane], ws.ray[5][lane]) };
                         }
                         live = false;
+                        if (SHADOWS && shadow_q) { // lit iff nothing is hit within the light's distance; then the next light
+                            shadow_q = false;
+                            Frame &f = frames[depth];
+                            const LightTerm lt = light_term(S, f.i, f.b, f.c);
+                            if (!(h.tri >= 0 && !(h.t * h.t > lt.r2)))
+                                f.a = f.a + ((f.g * lt.intensity) / lt.area) * lt.cos_law;
+                            ++f.i;
+                            if (f.i < S.n_lights) {
+                                ray = Ray{ f.b + f.c * P.shadow_bias, light_term(S, f.i, f.b, f.c).dir };
+                                act = 3;
+                            } else {
+                                c = f.a / gi_div;
+                                act = 2;
+                            }
+                            continue;
+                        }
                         act = 2;
                         if (h.tri < 0) {
                             c = bg;
@@ -328,6 +382,11 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                                 f.a = mk(0.0f, 0.0f, 0.0f), f.b = s.P, f.c = s.n, f.e = ray.d, f.g = albedo;
                                 ray = Ray{ s.P + s.n * P.diffuse_reflection_bias, gi_direction(ray.d, s.n, rng) };
                                 ++depth, act = 1;
+                            } else if (SHADOWS && P.shadows && S.n_lights > 0) {
+                                f.kind = kDirectShadow, f.i = 0;
+                                f.a = mk(0.0f, 0.0f, 0.0f), f.b = s.P, f.c = s.n, f.g = albedo;
+                                ray = Ray{ s.P + s.n * P.shadow_bias, light_term(S, 0, s.P, s.n).dir };
+                                act = 3;
                             } else {
                                 c = add_direct_light(S, mk(0.0f, 0.0f, 0.0f), s, albedo, no_shadow) / gi_div;
                             }
@@ -392,6 +451,13 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                         if (uint32_t(++f.i) < P.gi_rays) {
                             ray = Ray{ f.b + f.c * P.diffuse_reflection_bias, gi_direction(f.e, f.c, rng) };
                             act = 1;
+                            continue;
+                        }
+                        if (SHADOWS && P.shadows && S.n_lights > 0) { // the light loop of this surface, one shadow query per light
+                            f.kind = kDirectShadow, f.i = 0; // a (GI sum so far), b, c, g stay
+                            --depth;
+                            ray = Ray{ f.b + f.c * P.shadow_bias, light_term(S, 0, f.b, f.c).dir };
+                            act = 3;
                             continue;
                         }
                         Surface s{};

@@ -146,7 +146,7 @@ typedef struct crt_cuda_ctx crt_cuda_ctx;
 #define CRT_TRAVERSAL_KD 1      /* front-to-back k-d interval traversal with strict pruning; same winners  */
 #define CRT_TRAVERSAL_BRUTE 2   /* every triangle in parse order (crt_intersection.cpp:95-107), checker only */
 
-#define CRT_PIPELINE_AUTO 0      /* wavefront (hybrid for depth >= 5 or band-sharded frames) without GI, persistent with GI, megakernel for shadow rays / literal GI */
+#define CRT_PIPELINE_AUTO 0      /* wavefront (hybrid for depth >= 5 or band-sharded frames); persistent with GI or shadow rays; megakernel for those under the literal traversal */
 #define CRT_PIPELINE_MEGAKERNEL 1 /* one thread per pixel evaluates the whole recursion depth-first     */
 #define CRT_PIPELINE_WAVEFRONT 2  /* ray queues + compaction between bounce stages (no GI)              */
 #define CRT_PIPELINE_HYBRID 4     /* primary level as wavefront kernels, all deeper levels in one persistent kernel (no GI) */

@@ -231,6 +231,15 @@ def test_persistent_pipeline_equals_the_other_pipelines_bit_for_bit(crt, ot, ren
             hyb, hyb8, st_h = renderer.render(crt.default_params(max_ray_depth=depth, collect_stats=1, pipeline=crt.PIPELINE_HYBRID))
             assert same_bits(hyb, pers) and np.array_equal(hyb8, pers8)
             assert st_h["rays"] == st_p["rays"] and st_h["rays_by_depth"] == st_p["rays_by_depth"]
+    # flagged shadow mode: one shadow query per light inside the pixel's recursion (after the GI children under GI)
+    mega, mega8, st_m = renderer.render(crt.default_params(shadows=1, collect_stats=1, pipeline=crt.PIPELINE_MEGAKERNEL))
+    pers, pers8, st_p = renderer.render(crt.default_params(shadows=1, collect_stats=1, pipeline=crt.PIPELINE_PERSISTENT))
+    assert same_bits(mega, pers) and np.array_equal(mega8, pers8)
+    assert st_m["rays"] == st_p["rays"] and st_m["shadow_rays"] == st_p["shadow_rays"]
+    dflt, _, _ = renderer.render(crt.default_params(shadows=1))
+    assert same_bits(dflt, pers)
+    want = ot.port_render(flat, crt.default_params(shadows=1), primary=False)
+    assert ppm_ok_fraction(pers8, want["rgb8"]) >= 0.999 and st_p["shadow_rays"] == want["stats"]["shadow_rays"]
     want = ot.port_render(flat, crt.default_params(), primary=False)
     pers, pers8, _ = renderer.render(crt.default_params(pipeline=crt.PIPELINE_PERSISTENT))
     assert ppm_ok_fraction(pers8, want["rgb8"]) >= 0.999
