@@ -40,6 +40,11 @@ struct crt_cuda_ctx {
     Counters *d_counters = nullptr;
     Counters *h_counters = nullptr; // pinned
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    // crt_cuda_render starts the float frame's device-to-host copy right after the level-0 shade (ev_primary), on
+    // copy_stream, under the deeper levels' kernels; rows holding non-terminal pixels are copied again after resolve
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_primary = nullptr;
+    bool arm_early_copy = false, early_recorded = false;
     int last_width = 0, last_rows = 0, last_launches = 0;
     bool last_stats = false;
 
@@ -243,7 +248,9 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
                 seed = std::max(1, std::atoi(v));
             seed = deeper ? std::min(seed, int(dp.max_ray_depth)) : 1;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
-                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, seed);
+                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, seed,
+                                             ctx->arm_early_copy ? ctx->ev_primary : nullptr);
+            ctx->early_recorded = ctx->arm_early_copy;
             ctx->last_wavefront = true;
             if (e != cudaSuccess)
                 return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
@@ -262,7 +269,9 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         } else if (pipeline == CRT_PIPELINE_WAVEFRONT) {
             int launches = 0;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
-                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves);
+                                             ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, 0,
+                                             ctx->arm_early_copy ? ctx->ev_primary : nullptr);
+            ctx->early_recorded = ctx->arm_early_copy;
             ctx->last_wavefront = true;
             if (e != cudaSuccess)
                 return fail(ctx, CRT_ERR_CUDA, cudaGetErrorString(e));
@@ -323,7 +332,9 @@ int crt_cuda_create(int device, crt_cuda_ctx **out) {
     crt_cuda_ctx *ctx = new crt_cuda_ctx;
     ctx->device = device;
     bool ok = cudaSetDevice(device) == cudaSuccess && cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaEventCreate(&ctx->ev_begin) == cudaSuccess && cudaEventCreate(&ctx->ev_end) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_primary, cudaEventDisableTiming) == cudaSuccess &&
               cudaMalloc(&ctx->d_counters, sizeof(Counters)) == cudaSuccess &&
               cudaHostAlloc(&ctx->h_counters, sizeof(Counters), cudaHostAllocDefault) == cudaSuccess;
     if (!ok) {
@@ -358,6 +369,10 @@ void crt_cuda_destroy(crt_cuda_ctx *ctx) {
         cudaEventDestroy(ctx->ev_begin);
     if (ctx->ev_end)
         cudaEventDestroy(ctx->ev_end);
+    if (ctx->ev_primary)
+        cudaEventDestroy(ctx->ev_primary);
+    if (ctx->copy_stream)
+        cudaStreamDestroy(ctx->copy_stream);
     if (ctx->own_stream)
         cudaStreamDestroy(ctx->own_stream);
     delete ctx;
@@ -516,14 +531,55 @@ int crt_cuda_synchronize(crt_cuda_ctx *ctx, crt_render_stats *stats) {
 int crt_cuda_render(crt_cuda_ctx *ctx, const crt_render_params *params, float *rgb_out, uint8_t *rgb8_out, crt_render_stats *stats) {
     if (!ctx)
         return CRT_ERR_INVALID;
-    if (int rc = enqueue_frame(ctx, params))
-        return rc;
+    // $CRT_EARLY_COPY=1 (wavefront and hybrid pipelines): every pixel whose primary ray ends on a terminal surface is
+    // final after the level-0 shade, so the float frame can start travelling there, on the copy engine, under the
+    // deeper levels' kernels; the rows that hold reflective / refractive pixels are then copied a second time after
+    // resolve.  Off by default: on B200 the overlapped copy (1.8 ms for a 4K float frame) stretches the walk kernels
+    // of C4 from 3.05 to 4.2 ms, so the frame reaches the host LATER than with the copy queued behind the kernels
+    // (5.03 vs 4.85 ms, tools/e2e_probe.py).
+    const char *early_env = std::getenv("CRT_EARLY_COPY");
+    const bool early_enabled = early_env && *early_env == '1';
+    ctx->arm_early_copy = rgb_out != nullptr && early_enabled;
+    ctx->early_recorded = false;
+    if (ctx->wf.h_flags)
+        ctx->wf.h_flags[1] = ctx->wf.h_flags[2] = 0;
+    const int enq = enqueue_frame(ctx, params);
+    ctx->arm_early_copy = false;
+    if (enq)
+        return enq;
     const size_t pixels = size_t(ctx->last_width) * size_t(ctx->last_rows);
-    if (rgb_out && pixels)
-        CRT_CK(ctx, cudaMemcpyAsync(rgb_out, ctx->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    const size_t row_floats = size_t(ctx->last_width) * 3;
+    const bool early = ctx->early_recorded && pixels;
+    if (rgb_out && pixels) {
+        if (early) {
+            CRT_CK(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_primary, 0));
+            CRT_CK(ctx, cudaMemcpyAsync(rgb_out, ctx->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->copy_stream));
+        } else {
+            CRT_CK(ctx, cudaMemcpyAsync(rgb_out, ctx->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    }
     if (rgb8_out && pixels)
         CRT_CK(ctx, cudaMemcpyAsync(rgb8_out, ctx->d_rgb8, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
-    return crt_cuda_synchronize(ctx, stats);
+    const int rc = crt_cuda_synchronize(ctx, stats);
+    if (early)
+        cudaStreamSynchronize(ctx->copy_stream);
+    if (rc)
+        return rc;
+    if (ctx->rerendered) { // the copies above carried the discarded frame
+        if (rgb_out && pixels)
+            CRT_CK(ctx, cudaMemcpyAsync(rgb_out, ctx->d_rgb, pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        if (rgb8_out && pixels)
+            CRT_CK(ctx, cudaMemcpyAsync(rgb8_out, ctx->d_rgb8, pixels * 3, cudaMemcpyDeviceToHost, ctx->stream));
+        CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    } else if (early && ctx->wf.h_flags && ctx->wf.h_flags[1] > 0) {
+        const int hi = std::min(ctx->wf.h_flags[1], ctx->last_rows), lo = std::max(0, 0x7fffffff - ctx->wf.h_flags[2]);
+        if (hi > lo) {
+            CRT_CK(ctx, cudaMemcpyAsync(rgb_out + size_t(lo) * row_floats, ctx->d_rgb + size_t(lo) * row_floats, size_t(hi - lo) * row_floats * sizeof(float),
+                                        cudaMemcpyDeviceToHost, ctx->stream));
+            CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+    }
+    return CRT_OK;
 }
 
 int crt_cuda_device_framebuffer(crt_cuda_ctx *ctx, void **rgb_dev, void **rgb8_dev, int *width, int *rows) {

@@ -22,6 +22,8 @@ struct WfCtl {                 // zeroed at the start of every frame
     int fetch[kMaxLevels];     // trace kernels' queue cursors
     int pending0;              // non-terminal pixels (entries of `pend`)
     int overflow;              // a level outgrew the pool: the host retries with a larger one
+    int pend_hi;               // 1 + highest local row holding a non-terminal pixel (0: none)
+    int pend_lo_inv;           // INT_MAX - lowest such row: both grow under atomicMax from the zeroed state
 };
 
 struct WfBuffers {
@@ -48,7 +50,7 @@ struct WavefrontState {
     size_t ray0_capacity = 0; // allocated entries of ray0_*
     size_t pend_capacity = 0;
     int sm_count = 0;
-    int *h_flags = nullptr;   // pinned: {overflow}
+    int *h_flags = nullptr;   // pinned: {overflow, pend_hi, pend_lo_inv}
     double grow = 1.0;        // pool = grow * pixels
 };
 
@@ -235,8 +237,16 @@ __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant_
         const unsigned pend_mask = __ballot_sync(0xffffffffu, level == 0 && children > 0);
         int pend_base = 0;
         if (pend_mask) {
-            if (lane == 0)
+            // rows that resolve will write again after this kernel: the host copies the frame out early and only
+            // these rows a second time (crt_cuda_render)
+            const bool pending = level == 0 && children > 0;
+            const int hi = __reduce_max_sync(0xffffffffu, pending ? ly + 1 : 0);
+            const int lo_inv = __reduce_max_sync(0xffffffffu, pending ? 0x7fffffff - ly : 0);
+            if (lane == 0) {
                 pend_base = atomicAdd(&ctl->pending0, __popc(pend_mask));
+                atomicMax(&ctl->pend_hi, hi);
+                atomicMax(&ctl->pend_lo_inv, lo_inv);
+            }
             pend_base = __shfl_sync(0xffffffffu, pend_base, 0);
         }
         if (!have)
@@ -315,9 +325,9 @@ inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
     if (!w.b.ctl) {
         if ((e = cudaMalloc(&w.b.ctl, sizeof(WfCtl))) != cudaSuccess)
             return e;
-        if ((e = cudaHostAlloc(&w.h_flags, sizeof(int), cudaHostAllocDefault)) != cudaSuccess)
+        if ((e = cudaHostAlloc(&w.h_flags, 3 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess)
             return e;
-        *w.h_flags = 0;
+        w.h_flags[0] = w.h_flags[1] = w.h_flags[2] = 0;
         cudaDeviceProp prop;
         int dev = 0;
         cudaGetDevice(&dev);
@@ -398,7 +408,7 @@ inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, con
 // `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_light instead of k_wf_trace
 inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
                                     uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves,
-                                    int first_levels_only = 0) {
+                                    int first_levels_only = 0, cudaEvent_t after_primary = nullptr) {
     const int patches_x = (S.cam.width + 7) / 8, patches_y = (dp.rows + 3) / 4;
     const int P = patches_x * patches_y * 32;
     secondary = secondary && dp.max_ray_depth > 0;
@@ -431,13 +441,16 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
         const int sb = level == 0 ? min(w.sm_count * 32, (P + kShadeBlock - 1) / kShadeBlock) : w.sm_count * 8;
         k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
         n += 2;
+        // every pixel whose primary ray ends in a terminal surface is final now; the rest are rewritten by resolve
+        if (level == 0 && after_primary && (e = cudaEventRecord(after_primary, stream)) != cudaSuccess)
+            return e;
     }
     for (int level = levels - 2; level >= 0 && first_levels_only <= 0; --level) {
         k_wf_resolve<<<w.sm_count * 4, 256, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
         ++n;
     }
     if (secondary)
-        e = cudaMemcpyAsync(w.h_flags, &w.b.ctl->overflow, sizeof(int), cudaMemcpyDeviceToHost, stream);
+        e = cudaMemcpyAsync(w.h_flags, &w.b.ctl->overflow, 3 * sizeof(int), cudaMemcpyDeviceToHost, stream);
     if (launches)
         *launches = n;
     return e != cudaSuccess ? e : cudaGetLastError();

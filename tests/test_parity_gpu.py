@@ -212,6 +212,31 @@ def test_pushed_bands_assemble_the_frame_on_rank0(crt, ot, renderer):
                     r.close()
 
 
+@pytest.mark.parametrize("rel", ["15-01-conclusion/scene1.crtscene", "11-01-refractive/scene8.crtscene", "09-02-diffuse-smooth-shading/scene2.crtscene"])
+@pytest.mark.parametrize("early", ["0", "1"])
+def test_host_frame_copied_under_the_deeper_levels_equals_the_device_frame(crt, ot, renderer, rel, early, monkeypatch):
+    """$CRT_EARLY_COPY=1: crt_cuda_render starts the float frame's device-to-host copy after the level-0 shade and
+    re-copies only the rows with reflective / refractive pixels after resolve: the host frame must equal the device
+    frame bit for bit, for pinned and pageable buffers, whole frames and row bands, in every pipeline"""
+    monkeypatch.setenv("CRT_EARLY_COPY", early)
+    import torch
+    from crt_b200 import distributed as D
+    scene, flat = load(crt, ot, rel, (322, 181))
+    renderer.upload(flat)
+    for pipeline in (crt.PIPELINE_WAVEFRONT, crt.PIPELINE_HYBRID, crt.PIPELINE_MEGAKERNEL):
+        for kw in ({}, {"rank": 1, "world": 3, "band_rows": 5}):
+            params = crt.default_params(pipeline=pipeline, max_ray_depth=6, **kw)
+            rows = len(crt.Renderer.owned_rows(181, params.rank, params.world, params.band_rows))
+            pinned = torch.empty((rows, 322, 3), dtype=torch.float32).pin_memory()
+            pinned.fill_(-1.0)
+            renderer.render(params, want_rgb8=False, rgb_out=pinned.numpy())
+            pageable, _, _ = renderer.render(params)
+            ptr, _, w, r = renderer.device_framebuffer()
+            assert (w, r) == (322, rows)
+            dev = D.wrap_device_bytes(ptr, w * r * 12, torch.device("cuda", 0)).cpu().numpy().view(np.float32).reshape(r, w, 3)
+            assert same_bits(pinned.numpy(), dev) and same_bits(pageable, dev)
+
+
 @pytest.mark.parametrize("rel", ["15-01-conclusion/scene2.crtscene", "15-01-conclusion/scene1.crtscene", "11-01-refractive/scene8.crtscene",
                                  "11-01-refractive/scene5.crtscene", "12-01-textures/scene4.crtscene", "14-01-acceleration-tree/scene0.crtscene"])
 def test_persistent_pipeline_equals_the_other_pipelines_bit_for_bit(crt, ot, renderer, rel):
