@@ -174,7 +174,7 @@ def run_ours(args):
     t0 = time.perf_counter()
     text, root = scene_text(args.workload)
     scene = crt.Scene.load_json(text, root)
-    flat = scene.flatten()
+    flat = scene.flatten(reference_tree=False)  # the timed path walks the SAH tree only (TRAVERSAL_KD)
     t_load = time.perf_counter() - t0
     renderer = crt.Renderer(local)
     stream = torch.cuda.current_stream(device)

@@ -20,12 +20,13 @@ LIB_PATH = os.environ.get("CRT_B200_LIB") or os.path.join(_HERE, "lib", "libcrt_
 CRT_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_IO, ERR_PARSE, ERR_NO_DEVICE = -1, -2, -3, -4, -5
 TRAVERSAL_LITERAL, TRAVERSAL_KD, TRAVERSAL_BRUTE = 0, 1, 2
+FLATTEN_REFERENCE_TREE = 1
 PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_PERSISTENT, PIPELINE_HYBRID = 0, 1, 2, 3, 4
 REF_CULL_BIT = 0x80000000
 
 # every symbol include/crt_cuda.h declares (tests check that the library exports each of them)
 EXPORTED_SYMBOLS = [
-    "crt_scene_load_file", "crt_scene_load_json", "crt_scene_flatten", "crt_scene_set_camera", "crt_scene_set_resolution",
+    "crt_scene_load_file", "crt_scene_load_json", "crt_scene_flatten", "crt_scene_flatten_ex", "crt_scene_set_camera", "crt_scene_set_resolution",
     "crt_scene_free", "crt_scene_last_error", "crt_render_params_default", "crt_cuda_device_count", "crt_cuda_create",
     "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_set_camera",
     "crt_cuda_render", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
@@ -111,6 +112,7 @@ def _load_library():
         "crt_scene_load_file": (C.c_int, [C.c_char_p, P(vp)]),
         "crt_scene_load_json": (C.c_int, [C.c_char_p, C.c_size_t, C.c_char_p, P(vp)]),
         "crt_scene_flatten": (C.c_int, [vp, P(FlatScene)]),
+        "crt_scene_flatten_ex": (C.c_int, [vp, C.c_int, P(FlatScene)]),
         "crt_scene_set_camera": (C.c_int, [vp, P(C.c_float), P(C.c_float), C.c_float]),
         "crt_scene_set_resolution": (C.c_int, [vp, C.c_int, C.c_int]),
         "crt_scene_free": (None, [vp]),
@@ -194,11 +196,13 @@ class Scene:
             raise CrtError(f"crt_scene_load_json -> {rc}: {lib.crt_scene_last_error().decode()}")
         return cls(h)
 
-    def flatten(self) -> FlatScene:
+    def flatten(self, reference_tree: bool = True) -> FlatScene:
+        """reference_tree=False (crt_scene_flatten_ex without CRT_FLATTEN_REFERENCE_TREE): neither builds nor uploads
+        the reference's acceleration tree; the scene then renders with TRAVERSAL_KD only"""
         flat = FlatScene()
-        rc = lib.crt_scene_flatten(self._h, C.byref(flat))
+        rc = lib.crt_scene_flatten_ex(self._h, FLATTEN_REFERENCE_TREE if reference_tree else 0, C.byref(flat))
         if rc != CRT_OK:
-            raise CrtError(f"crt_scene_flatten -> {rc}")
+            raise CrtError(f"crt_scene_flatten_ex -> {rc}")
         flat._owner = self  # the arrays live in the scene handle: keep it alive as long as the view
         self._flat = flat
         return flat

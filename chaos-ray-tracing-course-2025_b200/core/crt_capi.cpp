@@ -54,18 +54,27 @@ int crt_scene_load_json(const char *json, size_t length, const char *asset_root,
     return load(std::string_view{ json, length }, std::filesystem::path{ asset_root ? asset_root : "" }, out);
 }
 
-int crt_scene_flatten(const crt_scene *scene, crt_flat_scene *out) {
+int crt_scene_flatten_ex(const crt_scene *scene, int flags, crt_flat_scene *out) {
     if (!scene || !out)
         return CRT_ERR_INVALID;
     crt_scene *mut = const_cast<crt_scene *>(scene);
+    const bool with_tree = (flags & CRT_FLATTEN_REFERENCE_TREE) != 0;
     if (!mut->flat_valid) {
-        crt::flatten_scene(mut->scene, mut->flat);
+        crt::flatten_scene(mut->scene, mut->flat, with_tree);
         mut->flat_valid = true;
+    } else if (with_tree) {
+        crt::add_reference_tree(mut->scene, mut->flat); // earlier views stay valid: only the tree arrays are filled in
     }
     mut->flat.view.camera = crt::flatten_camera(mut->scene.camera);
     *out = mut->flat.view;
+    if (!with_tree) { // a view without the reference tree, whatever an earlier call built
+        out->n_nodes = 0, out->n_refs = 0, out->max_depth = 0;
+        out->box_nodes = nullptr, out->kd_nodes = nullptr, out->refs = nullptr;
+    }
     return CRT_OK;
 }
+
+int crt_scene_flatten(const crt_scene *scene, crt_flat_scene *out) { return crt_scene_flatten_ex(scene, CRT_FLATTEN_REFERENCE_TREE, out); }
 
 int crt_scene_set_camera(crt_scene *scene, const float position[3], const float rotation[9], float fov_degrees) {
     if (!scene || !position || !rotation)

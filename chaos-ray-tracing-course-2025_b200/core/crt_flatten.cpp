@@ -197,7 +197,7 @@ FastTreeStats build_fast_tree(const AccelerationTree &tree, const std::vector<Tr
     return stats;
 }
 
-void flatten_scene(const Scene &scene, FlatScene &out) {
+void flatten_scene(const Scene &scene, FlatScene &out, bool with_reference_tree) {
     out = FlatScene{};
     const size_t n_tri = scene.triangles.size(), n_vert = scene.vertices.size();
 
@@ -224,32 +224,6 @@ void flatten_scene(const Scene &scene, FlatScene &out) {
         out.vert_normal[i] = { v.normal.x, v.normal.y, v.normal.z, 0.0f };
         out.vert_uv[2 * i] = v.uv.x; // uv.z is interpolated by the reference but never read (crt_texture.cpp:29-44)
         out.vert_uv[2 * i + 1] = v.uv.y;
-    }
-
-    const AccelerationTree &tree = scene.acceleration_tree;
-    out.box_nodes.resize(tree.size());
-    out.kd_nodes.resize(tree.size());
-    for (size_t i = 0; i < tree.size(); ++i) {
-        const AccelerationTreeNode &n = tree[i];
-        crt_box_node &b = out.box_nodes[i];
-        std::memcpy(b.min, n.bounds.min.data, 12);
-        std::memcpy(b.max, n.bounds.max.data, 12);
-        crt_kd_node &k = out.kd_nodes[i];
-        if (n.is_leaf()) {
-            b.left = -n.first_reference - 2;
-            b.right = n.reference_count;
-            k = { 0.0f, n.first_reference, n.reference_count, 3 };
-        } else {
-            b.left = n.children_indices[0];
-            b.right = n.children_indices[1];
-            const int axis = n.depth % 3;
-            k = { (n.bounds.min.data[axis] + n.bounds.max.data[axis]) * 0.5f, n.children_indices[0], n.children_indices[1], axis };
-        }
-    }
-    out.refs.resize(tree.references.size());
-    for (size_t i = 0; i < out.refs.size(); ++i) {
-        const uint32_t t = tree.references[i];
-        out.refs[i] = t | (scene.triangles[t].flags.back_face_culling ? CRT_REF_CULL_BIT : 0u);
     }
 
     for (const Light &l : scene.lights)
@@ -279,24 +253,29 @@ void flatten_scene(const Scene &scene, FlatScene &out) {
     v.reflections_on = scene.reflections_on;
     v.refractions_on = scene.refractions_on;
     v.bucket_size = scene.bucket_size;
-    if (!tree.empty()) {
-        std::memcpy(v.root_min, tree[0].bounds.min.data, 12);
-        std::memcpy(v.root_max, tree[0].bounds.max.data, 12);
+    // root box = min / max over every triangle vertex, starting from the empty box (crt_acceleration_tree.cpp:89-94)
+    AABB root = AABB::vacuum();
+    for (size_t i = 0; i < 3 * n_tri; ++i) {
+        const crt_float4 &p = out.tri_verts[i];
+        root.min.x = std::min(root.min.x, p.x), root.min.y = std::min(root.min.y, p.y), root.min.z = std::min(root.min.z, p.z);
+        root.max.x = std::max(root.max.x, p.x), root.max.y = std::max(root.max.y, p.y), root.max.z = std::max(root.max.z, p.z);
     }
+    std::memcpy(v.root_min, root.min.data, 12);
+    std::memcpy(v.root_max, root.max.data, 12);
     v.n_triangles = int32_t(n_tri);
     v.n_vertices = int32_t(n_vert);
-    v.n_nodes = int32_t(tree.size());
-    v.n_refs = int32_t(out.refs.size());
     v.n_lights = int32_t(out.lights.size());
     v.n_materials = int32_t(out.materials.size());
     v.n_textures = int32_t(out.textures.size());
     v.n_texels = int32_t(out.texels.size());
-    v.max_depth = tree.max_depth;
     // the walk tree: an SAH k-d tree of our own (crt_kdbuild.cpp) unless CRT_WALK_TREE=reference asks for the
     // reference's tree with the non-paying splits merged (build_fast_tree above)
     const char *which = std::getenv("CRT_WALK_TREE");
-    if (which && std::strcmp(which, "reference") == 0) {
-        const FastTreeStats fast = build_fast_tree(tree, scene.triangles, out);
+    const bool walk_reference = which && std::strcmp(which, "reference") == 0;
+    if (with_reference_tree || walk_reference)
+        add_reference_tree(scene, out);
+    if (walk_reference) {
+        const FastTreeStats fast = build_fast_tree(scene.reference_tree(), scene.triangles, out);
         v.fast_max_depth = fast.max_depth;
         v.n_fast_nodes = fast.nodes;
         v.n_fast_refs = fast.refs;
@@ -316,13 +295,48 @@ void flatten_scene(const Scene &scene, FlatScene &out) {
     v.tri_meta = out.tri_meta.data();
     v.vert_normal = out.vert_normal.data();
     v.vert_uv = out.vert_uv.data();
-    v.box_nodes = out.box_nodes.data();
-    v.kd_nodes = out.kd_nodes.data();
-    v.refs = out.refs.data();
     v.lights = out.lights.data();
     v.materials = out.materials.data();
     v.textures = out.textures.data();
     v.texels = out.texels.data();
+}
+
+void add_reference_tree(const Scene &scene, FlatScene &out) {
+    if (!out.box_nodes.empty())
+        return;
+    const AccelerationTree &tree = scene.reference_tree();
+    out.box_nodes.resize(tree.size());
+    out.kd_nodes.resize(tree.size());
+    for (size_t i = 0; i < tree.size(); ++i) {
+        const AccelerationTreeNode &n = tree[i];
+        crt_box_node &b = out.box_nodes[i];
+        std::memcpy(b.min, n.bounds.min.data, 12);
+        std::memcpy(b.max, n.bounds.max.data, 12);
+        crt_kd_node &k = out.kd_nodes[i];
+        if (n.is_leaf()) {
+            b.left = -n.first_reference - 2;
+            b.right = n.reference_count;
+            k = { 0.0f, n.first_reference, n.reference_count, 3 };
+        } else {
+            b.left = n.children_indices[0];
+            b.right = n.children_indices[1];
+            const int axis = n.depth % 3;
+            k = { (n.bounds.min.data[axis] + n.bounds.max.data[axis]) * 0.5f, n.children_indices[0], n.children_indices[1], axis };
+        }
+    }
+    out.refs.resize(tree.references.size());
+    for (size_t i = 0; i < out.refs.size(); ++i) {
+        const uint32_t t = tree.references[i];
+        out.refs[i] = t | (scene.triangles[t].flags.back_face_culling ? CRT_REF_CULL_BIT : 0u);
+    }
+
+    crt_flat_scene &v = out.view;
+    v.n_nodes = int32_t(tree.size());
+    v.n_refs = int32_t(out.refs.size());
+    v.max_depth = tree.max_depth;
+    v.box_nodes = out.box_nodes.data();
+    v.kd_nodes = out.kd_nodes.data();
+    v.refs = out.refs.data();
 }
 
 } // namespace crt

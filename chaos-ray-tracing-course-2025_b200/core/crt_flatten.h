@@ -27,7 +27,12 @@ struct FlatScene {
 };
 
 crt_camera flatten_camera(const Camera &camera);
-void flatten_scene(const Scene &scene, FlatScene &out);
+// with_reference_tree = false leaves box_nodes / kd_nodes / refs empty (n_nodes == 0): enough for CRT_TRAVERSAL_KD, and
+// it skips the build and the upload of the reference's tree (6.6 M nodes / 38 M references for the 1 M-triangle
+// scene); $CRT_WALK_TREE=reference needs that tree and forces it.  add_reference_tree fills it in later without
+// touching the other arrays.
+void flatten_scene(const Scene &scene, FlatScene &out, bool with_reference_tree = true);
+void add_reference_tree(const Scene &scene, FlatScene &out);
 
 // Derives the walk tree from the reference tree (crt_flatten.cpp); exposed for tests.
 struct FastTreeStats {

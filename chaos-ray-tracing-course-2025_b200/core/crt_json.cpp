@@ -326,7 +326,7 @@ std::optional<Scene> read_scene_from_memory(std::string_view text, const std::fi
     Scene scene{ background, *camera };
     if (!read_meshes(doc.find("objects"), materials, scene.vertices, scene.triangles))
         return std::nullopt;
-    scene.acceleration_tree = acceleration_tree::build(scene.vertices, scene.triangles);
+    // the reference builds its tree here (crt_json.cpp:606); ours is built on first use (Scene::reference_tree)
 
     if (!read_lights(doc.find("lights"), scene.lights))
         return std::nullopt;

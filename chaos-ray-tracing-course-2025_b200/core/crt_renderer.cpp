@@ -47,6 +47,9 @@ std::vector<int> env_devices() {
     return out;
 }
 
+// the reference's tree is built, flattened and uploaded only when the literal traversal is asked for
+bool wants_reference_tree() { return env_int("CRT_TRAVERSAL", CRT_TRAVERSAL_KD) == CRT_TRAVERSAL_LITERAL; }
+
 DeviceScene &device_scene(const Scene &scene) {
     if (scene.device)
         return *scene.device;
@@ -56,7 +59,7 @@ DeviceScene &device_scene(const Scene &scene) {
         if (rc != CRT_OK)
             throw std::runtime_error("crt::render_image: cannot create CUDA contexts with peer access for $CRT_DEVICES (code " + std::to_string(rc) +
                                      "); this build renders on the GPU only");
-        flatten_scene(scene, dev->flat);
+        flatten_scene(scene, dev->flat, wants_reference_tree());
         if (crt_cuda_group_upload_scene(dev->group, &dev->flat.view) != CRT_OK)
             throw std::runtime_error(std::string("crt::render_image: scene upload failed: ") + crt_cuda_group_last_error(dev->group));
         scene.device = std::move(dev);
@@ -66,7 +69,7 @@ DeviceScene &device_scene(const Scene &scene) {
     if (rc != CRT_OK)
         throw std::runtime_error("crt::render_image: cannot create a CUDA context (code " + std::to_string(rc) +
                                  "); this build renders on the GPU only");
-    flatten_scene(scene, dev->flat);
+    flatten_scene(scene, dev->flat, wants_reference_tree());
     if (crt_cuda_upload_scene(dev->ctx, &dev->flat.view) != CRT_OK)
         throw std::runtime_error(std::string("crt::render_image: scene upload failed: ") + crt_cuda_last_error(dev->ctx));
     scene.device = std::move(dev);

@@ -157,7 +157,14 @@ struct Scene {
     Camera camera;
     std::vector<Vertex> vertices;
     std::vector<Triangle> triangles; // parse order (the reference moves these into the tree)
-    AccelerationTree acceleration_tree;
+    // the reference's acceleration tree (crt_acceleration_tree.cpp), built on first use: only CRT_TRAVERSAL_LITERAL
+    // and CRT_WALK_TREE=reference read it, the default walk uses the SAH tree of crt_kdbuild.cpp
+    const AccelerationTree &reference_tree() const {
+        if (!m_reference_tree)
+            m_reference_tree = std::make_shared<const AccelerationTree>(acceleration_tree::build(vertices, triangles));
+        return *m_reference_tree;
+    }
+    mutable std::shared_ptr<const AccelerationTree> m_reference_tree;
     std::vector<Light> lights;
     std::vector<Texture> textures;
     std::vector<Material> materials;

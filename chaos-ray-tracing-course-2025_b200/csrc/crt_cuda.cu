@@ -179,6 +179,8 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         return fail(ctx, CRT_ERR_INVALID, "params is NULL");
     if (params->traversal != CRT_TRAVERSAL_LITERAL && params->traversal != CRT_TRAVERSAL_KD)
         return fail(ctx, CRT_ERR_INVALID, "render supports CRT_TRAVERSAL_LITERAL or CRT_TRAVERSAL_KD (brute force is a primary-hit checker only)");
+    if (params->traversal == CRT_TRAVERSAL_LITERAL && ctx->scene.n_nodes < 1)
+        return fail(ctx, CRT_ERR_INVALID, "CRT_TRAVERSAL_LITERAL needs the reference's acceleration tree: flatten the scene with CRT_FLATTEN_REFERENCE_TREE");
     if (params->world > 1 && (params->rank < 0 || params->rank >= params->world))
         return fail(ctx, CRT_ERR_INVALID, "rank outside [0, world)");
     CRT_CK(ctx, cudaSetDevice(ctx->device));
@@ -392,8 +394,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         return CRT_ERR_INVALID;
     if (!s)
         return fail(ctx, CRT_ERR_INVALID, "scene is NULL");
-    if (s->n_nodes < 1 || !s->box_nodes || !s->kd_nodes)
-        return fail(ctx, CRT_ERR_INVALID, "scene has no acceleration tree");
+    // n_nodes == 0: flattened without the reference's tree (crt_scene_flatten_ex); CRT_TRAVERSAL_LITERAL is then refused
+    if (s->n_nodes < 0 || (s->n_nodes > 0 && !s->box_nodes))
+        return fail(ctx, CRT_ERR_INVALID, "scene has a broken acceleration tree");
     if (s->n_fast_nodes < 1 || !s->fast_nodes)
         return fail(ctx, CRT_ERR_INVALID, "scene has no walk tree (fast_nodes)");
     if (s->max_depth + 2 > kStack || s->fast_max_depth + 2 > kStack)
@@ -624,6 +627,8 @@ int crt_cuda_primary_hits(crt_cuda_ctx *ctx, int traversal, int32_t *tri_id, flo
         return fail(ctx, CRT_ERR_INVALID, "no scene uploaded");
     if (traversal < CRT_TRAVERSAL_LITERAL || traversal > CRT_TRAVERSAL_BRUTE)
         return fail(ctx, CRT_ERR_INVALID, "unknown traversal");
+    if (traversal == CRT_TRAVERSAL_LITERAL && ctx->scene.n_nodes < 1)
+        return fail(ctx, CRT_ERR_INVALID, "CRT_TRAVERSAL_LITERAL needs the reference's acceleration tree: flatten the scene with CRT_FLATTEN_REFERENCE_TREE");
     CRT_CK(ctx, cudaSetDevice(ctx->device));
     const int W = ctx->scene.cam.width, H = ctx->scene.cam.height;
     const size_t n = size_t(W) * H;

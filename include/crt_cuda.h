@@ -129,8 +129,13 @@ typedef struct crt_scene crt_scene;
 
 int crt_scene_load_file(const char *path, crt_scene **out);
 int crt_scene_load_json(const char *json, size_t length, const char *asset_root, crt_scene **out);
-/* pointers inside *out stay valid until crt_scene_free */
+/* pointers inside *out stay valid until crt_scene_free.  crt_scene_flatten includes the reference's acceleration tree
+ * (box_nodes / kd_nodes / refs, src/core/crt_acceleration_tree.cpp:31-106), which CRT_TRAVERSAL_LITERAL walks;
+ * crt_scene_flatten_ex without CRT_FLATTEN_REFERENCE_TREE leaves it out (n_nodes == 0): the scene then renders with
+ * CRT_TRAVERSAL_KD only and skips the build and the upload of that tree (0.47 GB of the 0.53 GB of the 1 M-triangle scene) */
+#define CRT_FLATTEN_REFERENCE_TREE 1
 int crt_scene_flatten(const crt_scene *scene, crt_flat_scene *out);
+int crt_scene_flatten_ex(const crt_scene *scene, int flags, crt_flat_scene *out);
 /* change the image size / camera after loading (orbit frames, 4K variants); rebuilds nothing else */
 int crt_scene_set_camera(crt_scene *scene, const float position[3], const float rotation[9], float fov_degrees);
 int crt_scene_set_resolution(crt_scene *scene, int width, int height);

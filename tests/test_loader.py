@@ -248,3 +248,26 @@ def test_sah_walk_tree_invariants(crt, ot, rel):
             todo.append((c1, l, chi, right, depth + 1))
     assert seen_nodes == len(fast) and max_depth == flat.fast_max_depth
     assert listed == set(range(flat.n_triangles)), "every triangle is reachable"
+
+
+@pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "11-01-refractive/scene3.crtscene"])
+def test_flatten_without_the_reference_tree(crt, ot, rel):
+    """crt_scene_flatten_ex without CRT_FLATTEN_REFERENCE_TREE: no reference tree (it is not even built), everything
+    else -- root box, triangles, walk tree -- identical; asking for the tree later fills it in and keeps the first view
+    valid"""
+    with open(ot.scene_file(rel)) as f:
+        text = f.read()
+    root = os.path.dirname(ot.scene_file(rel))
+    lean_scene, full_scene = crt.Scene.load_json(text, root), crt.Scene.load_json(text, root)
+    lean, full = lean_scene.flatten(reference_tree=False), full_scene.flatten()
+    assert lean.n_nodes == 0 and lean.n_refs == 0 and lean.max_depth == 0 and full.n_nodes > 0
+    assert list(lean.root_min) == list(full.root_min) and list(lean.root_max) == list(full.root_max)
+    a, b = lean.arrays(), full.arrays()
+    for key in ("tri_verts", "tri_meta", "vert_normal", "vert_uv", "fast_nodes", "fast_refs", "lights", "materials", "textures", "texels"):
+        assert np.array_equal(otools.bits(a[key]) if a[key].dtype == np.float32 else a[key], otools.bits(b[key]) if b[key].dtype == np.float32 else b[key]), key
+    later = lean_scene.flatten()  # upgrade in place
+    c = later.arrays()
+    for key in ("box_nodes", "kd_nodes", "refs"):
+        assert np.array_equal(c[key], b[key]), key
+    assert later.n_nodes == full.n_nodes and later.max_depth == full.max_depth
+    assert np.array_equal(lean.arrays()["fast_nodes"], b["fast_nodes"])  # the first view still reads the same arrays

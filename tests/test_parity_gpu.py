@@ -321,3 +321,22 @@ def test_device_group_renders_the_frame(crt, ot, renderer, n_devices):
             assert np.array_equal(only8, want8)
         finally:
             group.close()
+
+
+def test_scene_flattened_without_the_reference_tree(crt, ot, renderer):
+    """the lean upload (no reference tree) renders bit-identically under TRAVERSAL_KD and refuses TRAVERSAL_LITERAL"""
+    rel = "15-01-conclusion/scene1.crtscene"
+    scene, flat = load(crt, ot, rel, (322, 181))
+    renderer.upload(flat)
+    want, want8, _ = renderer.render(crt.default_params())
+    hits = renderer.primary_hits(crt.TRAVERSAL_KD)
+    lean = scene.flatten(reference_tree=False)
+    assert lean.n_nodes == 0
+    renderer.upload(lean)
+    got, got8, _ = renderer.render(crt.default_params())
+    assert same_bits(got, want) and np.array_equal(got8, want8)
+    assert np.array_equal(renderer.primary_hits(crt.TRAVERSAL_KD)[0], hits[0])
+    with pytest.raises(crt.CrtError, match="reference's acceleration tree"):
+        renderer.render(crt.default_params(traversal=crt.TRAVERSAL_LITERAL))
+    with pytest.raises(crt.CrtError, match="reference's acceleration tree"):
+        renderer.primary_hits(crt.TRAVERSAL_LITERAL)

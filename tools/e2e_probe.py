@@ -18,7 +18,7 @@ desc, W, H, depth, _ = bench.WORKLOADS[workload]
 text, root = bench.scene_text(workload)
 scene = crt.Scene.load_json(text, root)
 r = crt.Renderer(0)
-r.upload(scene)
+r.upload(scene.flatten(reference_tree=False))
 p = crt.default_params(max_ray_depth=depth)
 host = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
 host8 = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory()

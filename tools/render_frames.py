@@ -20,7 +20,7 @@ desc, W, H, depth, _ = bench.WORKLOADS[workload]
 text, root = bench.scene_text(workload)
 scene = crt.Scene.load_json(text, root)
 r = crt.Renderer(0)
-flat = r.upload(scene)
+flat = r.upload(scene.flatten(reference_tree=traversal == "literal"))
 p = crt.default_params(max_ray_depth=depth, collect_stats=stats,
                        pipeline={"auto": 0, "mega": 1, "wavefront": 2, "persistent": 3, "hybrid": 4}[pipeline], traversal={"kd": 1, "literal": 0}[traversal])
 for i in range(frames):
