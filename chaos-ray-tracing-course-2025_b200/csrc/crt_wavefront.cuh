@@ -291,6 +291,10 @@ __device__ __forceinline__ V3 combine(const WfBuffers &b, const int4 rec, int no
 __global__ void __launch_bounds__(256) k_wf_resolve(const __grid_constant__ DScene S, const __grid_constant__ DParams P, const __grid_constant__ WfBuffers b,
                                                     int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
     const WfCtl *ctl = b.ctl;
+    // a level outgrew the pool: the host discards this frame and renders it again.  Nothing to resolve -- and `pend`
+    // has holes (pending0 counts the pixels whose children did not fit, their entries were never written)
+    if (ctl->overflow)
+        return;
     if (level == 0) {
         const int total = ctl->pending0;
         for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < total; k += gridDim.x * blockDim.x) {

@@ -1,6 +1,7 @@
 """Parity tests proper (-m gpu): the CUDA path, called through the C ABI, against the oracle on the same inputs.
 Bars (BASELINE.json): same primary hit triangle on >= 99.99 % of rays; PPM channel difference <= 1/255 on >= 99.9 %
 of pixels.  Where no libm function is involved we additionally demand BIT-IDENTICAL float framebuffers."""
+import json
 import os
 
 import numpy as np
@@ -340,3 +341,33 @@ def test_scene_flattened_without_the_reference_tree(crt, ot, renderer):
         renderer.render(crt.default_params(traversal=crt.TRAVERSAL_LITERAL))
     with pytest.raises(crt.CrtError, match="reference's acceleration tree"):
         renderer.primary_hits(crt.TRAVERSAL_LITERAL)
+
+
+@pytest.mark.parametrize("early", ["0", "1"])
+def test_ray_pool_overflow_renders_the_frame_again(crt, ot, early, monkeypatch):
+    """two refractive sheets filling the view: level 1 holds 2 rays per pixel and level 2 about as many again, so a
+    fresh context (pool = 1x pixels) overflows twice, grows the pool and renders the frame again; the host buffers
+    must carry the final frame, identical to the per-pixel kernel's, which has no pool"""
+    monkeypatch.setenv("CRT_EARLY_COPY", early)
+    quad = lambda z, m=0, r=30: {"material_index": m, "vertices": [-r, -r, z, r, -r, z, r, r, z, -r, r, z], "triangles": [0, 1, 2, 0, 2, 3]}
+    doc = {"settings": {"background_color": [0.2, 0.4, 0.6], "image_settings": {"width": 160, "height": 96}},
+           "camera": {"matrix": [1, 0, 0, 0, 1, 0, 0, 0, 1], "position": [0, 0, 0]},
+           "lights": [{"intensity": 100, "position": [0, 5, 0]}],
+           "materials": [{"type": "refractive", "ior": 1.5, "smooth_shading": False},
+                         {"type": "diffuse", "albedo": [0.9, 0.5, 0.3], "smooth_shading": False}],
+           "objects": [quad(-2.0), quad(-3.0), quad(-6.0, 1, 4)]}
+    scene = crt.Scene.load_json(json.dumps(doc))
+    flat = scene.flatten()
+    fresh = crt.Renderer(0)
+    try:
+        fresh.upload(flat)
+        params = dict(max_ray_depth=4, collect_stats=1)
+        for pipeline in (crt.PIPELINE_WAVEFRONT, crt.PIPELINE_HYBRID):
+            got, got8, stats = fresh.render(crt.default_params(pipeline=pipeline, **params))
+            want, want8, wstats = fresh.render(crt.default_params(pipeline=crt.PIPELINE_MEGAKERNEL, **params))
+            assert stats["rays_by_depth"][1] > 160 * 96 and stats["rays"] == wstats["rays"]
+            assert same_bits(got, want) and np.array_equal(got8, want8)
+            oracle = ot.port_render(flat, crt.default_params(**params), primary=False)
+            assert same_bits(got, oracle["rgb"])
+    finally:
+        fresh.close()
