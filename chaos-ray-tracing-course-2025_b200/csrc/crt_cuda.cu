@@ -181,6 +181,10 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         return fail(ctx, CRT_ERR_INVALID, "render supports CRT_TRAVERSAL_LITERAL or CRT_TRAVERSAL_KD (brute force is a primary-hit checker only)");
     if (params->traversal == CRT_TRAVERSAL_LITERAL && ctx->scene.n_nodes < 1)
         return fail(ctx, CRT_ERR_INVALID, "CRT_TRAVERSAL_LITERAL needs the reference's acceleration tree: flatten the scene with CRT_FLATTEN_REFERENCE_TREE");
+    // the recursion state (frames of the per-pixel kernels, levels of the wavefront) is sized for depths 0 .. 15; the
+    // reference has no limit, so a deeper request is refused rather than rendered differently
+    if (params->max_ray_depth > uint32_t(kMaxDepthCap))
+        return fail(ctx, CRT_ERR_INVALID, "max_ray_depth above 15 is not supported by this build (CRT_MAX_RAY_DEPTH_LIMIT)");
     if (params->world > 1 && (params->rank < 0 || params->rank >= params->world))
         return fail(ctx, CRT_ERR_INVALID, "rank outside [0, world)");
     CRT_CK(ctx, cudaSetDevice(ctx->device));

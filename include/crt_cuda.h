@@ -158,8 +158,9 @@ typedef struct crt_cuda_ctx crt_cuda_ctx;
 #define CRT_PIPELINE_PERSISTENT 3 /* one persistent kernel: a lane keeps its pixel through the recursion, warp-cooperative walk (GI too) */
 
 /* crt::RendererSettings (src/core/crt_renderer.h:18-25) + the knobs that are new on this side */
+#define CRT_MAX_RAY_DEPTH_LIMIT 15 /* the reference recurses without limit; the device's recursion state is sized for 0 .. 15 */
 typedef struct crt_render_params {
-    uint32_t max_ray_depth;                /* default 3  */
+    uint32_t max_ray_depth;                /* default 3; values above CRT_MAX_RAY_DEPTH_LIMIT are refused (CRT_ERR_INVALID) */
     uint32_t diffuse_reflection_ray_count; /* default 4  */
     float shadow_bias, reflection_bias, diffuse_reflection_bias, refraction_bias; /* default 1e-2 each */
     int32_t traversal;   /* CRT_TRAVERSAL_*  */

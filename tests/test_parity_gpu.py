@@ -371,3 +371,18 @@ def test_ray_pool_overflow_renders_the_frame_again(crt, ot, early, monkeypatch):
             assert same_bits(got, oracle["rgb"])
     finally:
         fresh.close()
+
+
+def test_deepest_supported_recursion_and_the_refusal_beyond_it(crt, ot, renderer):
+    """max_ray_depth 15 is the last depth the device's recursion state holds: every pipeline must still match the oracle
+    there (mirrors facing mirrors: 09-03, refraction chains: 11-01), and 16 must be refused, not clamped"""
+    for rel in ("09-03-reflective/scene5.crtscene", "11-01-refractive/scene8.crtscene"):
+        scene, flat = load(crt, ot, rel, (160, 90))
+        renderer.upload(flat)
+        want = ot.port_render(flat, crt.default_params(max_ray_depth=15, collect_stats=1), primary=False)
+        for pipeline in (crt.PIPELINE_MEGAKERNEL, crt.PIPELINE_WAVEFRONT, crt.PIPELINE_PERSISTENT, crt.PIPELINE_HYBRID):
+            got, _, stats = renderer.render(crt.default_params(max_ray_depth=15, pipeline=pipeline, collect_stats=1))
+            assert same_bits(got, want["rgb"]), (rel, pipeline)
+            assert stats["rays_by_depth"] == want["stats"]["rays_by_depth"], (rel, pipeline)
+    with pytest.raises(crt.CrtError, match="max_ray_depth above 15"):
+        renderer.render(crt.default_params(max_ray_depth=16))
