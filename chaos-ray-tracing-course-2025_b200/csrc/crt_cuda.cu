@@ -29,6 +29,7 @@ struct crt_cuda_ctx {
     DScene scene{};
     bool have_scene = false;
     bool has_secondary = false; // some material can spawn reflection / refraction rays
+    int bucket_size = 0;        // Scene::bucket_size: only decides whether the frame gets any bucket at all (enqueue_frame)
     bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
     crt_render_params last_params{};
     bool last_wavefront = false;
@@ -202,7 +203,16 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     if (stats)
         CRT_CK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), ctx->stream));
     CRT_CK(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
-    if (dp.rows > 0 && W > 0) {
+    // render_image cuts the frame into int(float(extent) / bucket_size + 0.5) buckets per axis, the last one absorbing
+    // the remainder (crt_renderer.cpp:160-170): an image narrower or lower than half a bucket gets NO bucket and
+    // stays the zero-initialised Image -- reproduced; otherwise the bucket size has no effect on the pixels
+    const auto bucket_count = [&](int extent) {
+        return ctx->bucket_size > 0 ? static_cast<int>(double(float(extent) / float(ctx->bucket_size)) + 0.5) : 0;
+    };
+    if (dp.rows > 0 && W > 0 && (bucket_count(W) <= 0 || bucket_count(H) <= 0)) {
+        CRT_CK(ctx, cudaMemsetAsync(ctx->d_rgb, 0, size_t(W) * size_t(dp.rows) * 3 * sizeof(float), ctx->stream));
+        CRT_CK(ctx, cudaMemsetAsync(ctx->d_rgb8, 0, size_t(W) * size_t(dp.rows) * 3, ctx->stream));
+    } else if (dp.rows > 0 && W > 0) {
         int pipeline = params->pipeline;
         const bool needs_mega = (ctx->scene.gi_on && dp.gi_rays > 0) || params->shadows;
         if (pipeline == CRT_PIPELINE_AUTO)
@@ -474,6 +484,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     d.textures = reinterpret_cast<const float4 *>(ctx->d_arena + parts[9].offset);
     d.texels = reinterpret_cast<const float4 *>(ctx->d_arena + parts[10].offset);
     d.kd_refs = reinterpret_cast<const uint32_t *>(ctx->d_arena + parts[11].offset);
+    ctx->bucket_size = s->bucket_size;
     ctx->has_secondary = false;
     for (int i = 0; i < s->n_materials; ++i)
         if ((s->materials[i].type == 1 && s->reflections_on) || (s->materials[i].type == 2 && s->refractions_on))

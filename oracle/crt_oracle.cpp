@@ -425,6 +425,21 @@ int crt_oracle_render(const crt_flat_scene *s, const crt_render_params *p, int t
     const unsigned n = threads > 0 ? unsigned(threads) : std::max(1u, std::thread::hardware_concurrency());
     std::vector<Stats> per_thread(n);
     const Ctx ctx{ *s, *p };
+    // bucket counts per axis, crt_renderer.cpp:160-161: int(float(extent) / bucket_size + 0.5); the last bucket of a row
+    // or column absorbs the remainder (:165-170), so the only effect on the pixels is that an image narrower or lower
+    // than half a bucket gets no bucket at all and stays the zero-initialised Image
+    const auto bucket_count = [&](int extent) { return s->bucket_size > 0 ? static_cast<int>(float(extent) / s->bucket_size + 0.5) : 0; };
+    if (bucket_count(W) <= 0 || bucket_count(s->camera.height) <= 0) {
+        if (rgb)
+            std::memset(rgb, 0, rows.size() * size_t(W) * 3 * sizeof(float));
+        if (rgb8)
+            std::memset(rgb8, 0, rows.size() * size_t(W) * 3);
+        if (stats) {
+            std::memset(stats, 0, sizeof *stats);
+            stats->rows_rendered = int(rows.size());
+        }
+        return 0;
+    }
     parallel_rows(int(rows.size()), int(n), [&](int local_row, int worker) {
         const int y = rows[size_t(local_row)];
         for (int x = 0; x < W; ++x) {

@@ -386,3 +386,21 @@ def test_deepest_supported_recursion_and_the_refusal_beyond_it(crt, ot, renderer
             assert stats["rays_by_depth"] == want["stats"]["rays_by_depth"], (rel, pipeline)
     with pytest.raises(crt.CrtError, match="max_ray_depth above 15"):
         renderer.render(crt.default_params(max_ray_depth=16))
+
+
+@pytest.mark.parametrize("size,bucket", [((10, 5), None), ((11, 40), None), ((12, 40), None), ((40, 11), None), ((30, 30), 64), ((32, 32), 64)])
+def test_images_below_half_a_bucket_stay_black_on_the_device_too(crt, ot, renderer, size, bucket):
+    """the reference's bucket grid leaves such images untouched (tests/test_oracle_pinned.py pins the port on this)"""
+    rel = "15-01-conclusion/scene1.crtscene"
+    doc = json.loads(ot.scene_variant(rel, *size))
+    if bucket is not None:
+        doc["settings"]["image_settings"]["bucket_size"] = bucket
+    scene = crt.Scene.load_json(json.dumps(doc), os.path.dirname(ot.scene_file(rel)))
+    flat = scene.flatten()
+    renderer.upload(flat)
+    want = ot.port_render(flat, crt.default_params(collect_stats=1), primary=False)
+    for pipeline in (crt.PIPELINE_AUTO, crt.PIPELINE_MEGAKERNEL, crt.PIPELINE_WAVEFRONT, crt.PIPELINE_PERSISTENT, crt.PIPELINE_HYBRID):
+        got, got8, stats = renderer.render(crt.default_params(pipeline=pipeline, collect_stats=1))
+        assert same_bits(got, want["rgb"]) and np.array_equal(got8, want["rgb8"]) and stats["rays"] == want["stats"]["rays"]
+    part, _, _ = renderer.render(crt.default_params(rank=1, world=2, band_rows=2))
+    assert same_bits(part, want["rgb"][crt.Renderer.owned_rows(size[1], 1, 2, 2)])
