@@ -150,7 +150,8 @@ __device__ __forceinline__ void write_pixel(const DScene &S, float *__restrict__
 constexpr int kShadeBlock = 128;
 
 __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
-                                                          const __grid_constant__ WfBuffers b, int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
+                                                          const __grid_constant__ WfBuffers b, int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
+                                                          bool track_rows) {
     WfCtl *ctl = b.ctl;
     const int start = level == 0 ? 0 : level_start(ctl, level);
     const int total = level == 0 ? b.P : level_count(ctl, b.cap, level, start);
@@ -239,14 +240,18 @@ __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant_
         if (pend_mask) {
             // rows that resolve will write again after this kernel: the host copies the frame out early and only
             // these rows a second time (crt_cuda_render)
-            const bool pending = level == 0 && children > 0;
-            const int hi = __reduce_max_sync(0xffffffffu, pending ? ly + 1 : 0);
-            const int lo_inv = __reduce_max_sync(0xffffffffu, pending ? 0x7fffffff - ly : 0);
-            if (lane == 0) {
-                pend_base = atomicAdd(&ctl->pending0, __popc(pend_mask));
-                atomicMax(&ctl->pend_hi, hi);
-                atomicMax(&ctl->pend_lo_inv, lo_inv);
+            // (only when the host asked for it: two atomics per warp on two hot words cost 0.06 ms of C4's frame)
+            if (track_rows) {
+                const bool pending = level == 0 && children > 0;
+                const int hi = __reduce_max_sync(0xffffffffu, pending ? ly + 1 : 0);
+                const int lo_inv = __reduce_max_sync(0xffffffffu, pending ? 0x7fffffff - ly : 0);
+                if (lane == 0) {
+                    atomicMax(&ctl->pend_hi, hi);
+                    atomicMax(&ctl->pend_lo_inv, lo_inv);
+                }
             }
+            if (lane == 0)
+                pend_base = atomicAdd(&ctl->pending0, __popc(pend_mask));
             pend_base = __shfl_sync(0xffffffffu, pend_base, 0);
         }
         if (!have)
@@ -443,7 +448,7 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
         else
             wavefront_launch_trace<CRT_TRAVERSAL_KD>(w, S, dp, stats, level, tb, counters, stream, light_leaves);
         const int sb = level == 0 ? min(w.sm_count * 32, (P + kShadeBlock - 1) / kShadeBlock) : w.sm_count * 8;
-        k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
+        k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8, level == 0 && after_primary != nullptr);
         n += 2;
         // every pixel whose primary ray ends in a terminal surface is final now; the rest are rewritten by resolve
         if (level == 0 && after_primary && (e = cudaEventRecord(after_primary, stream)) != cudaSuccess)
