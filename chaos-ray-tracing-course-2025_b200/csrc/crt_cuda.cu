@@ -31,6 +31,8 @@ struct crt_cuda_ctx {
     bool has_secondary = false; // some material can spawn reflection / refraction rays
     int bucket_size = 0;        // Scene::bucket_size: only decides whether the frame gets any bucket at all (enqueue_frame)
     bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
+    int packet_mode = -1;        // primary level as warp packets (crt_trace_packet.cuh): -1 by pixels per triangle, 0 / 1 = $CRT_PACKET
+    bool packet_primary = false; // this frame's decision
     crt_render_params last_params{};
     bool last_wavefront = false;
     bool rerendered = false; // crt_cuda_synchronize had to render the frame again (a bounce level outgrew the ray pool)
@@ -195,6 +197,8 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         return rc;
     const bool stats = params->collect_stats != 0;
     ctx->last_stats = stats;
+    ctx->packet_primary = ctx->packet_mode >= 0 ? ctx->packet_mode == 1
+                                                : ctx->scene.n_triangles > 0 && double(W) * double(H) / double(ctx->scene.n_triangles) >= 256.0;
     ctx->last_width = W;
     ctx->last_rows = dp.rows;
     ctx->last_launches = 0;
@@ -265,7 +269,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
             seed = deeper ? std::min(seed, int(dp.max_ray_depth)) : 1;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
                                              ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, seed,
-                                             ctx->arm_early_copy ? ctx->ev_primary : nullptr);
+                                             ctx->arm_early_copy ? ctx->ev_primary : nullptr, ctx->packet_primary);
             ctx->early_recorded = ctx->arm_early_copy;
             ctx->last_wavefront = true;
             if (e != cudaSuccess)
@@ -286,7 +290,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
             int launches = 0;
             cudaError_t e = wavefront_render(ctx->wf, ctx->scene, dp, params->traversal, stats, ctx->has_secondary, ctx->d_rgb, ctx->d_rgb8,
                                              ctx->d_counters, ctx->stream, &launches, ctx->light_leaves, 0,
-                                             ctx->arm_early_copy ? ctx->ev_primary : nullptr);
+                                             ctx->arm_early_copy ? ctx->ev_primary : nullptr, ctx->packet_primary);
             ctx->early_recorded = ctx->arm_early_copy;
             ctx->last_wavefront = true;
             if (e != cudaSuccess)
@@ -496,6 +500,13 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     ctx->light_leaves = leaves > 0 && double(s->n_fast_refs) / double(leaves) <= 6.0;
     if (const char *k = std::getenv("CRT_TRACE_KERNEL"); k && *k)
         ctx->light_leaves = std::strcmp(k, "light") == 0;
+    // primary level as warp packets (crt_trace_packet.cuh): pays when a patch of 32 pixels sees few triangles -- the
+    // rays of a warp then share their nodes and leaves.  Measured on B200 (tools/packet_sweep.py, profiles/
+    // r1z_packet_sweep.txt): ahead of the per-lane walk from ~130-500 pixels per triangle upwards (C3 0.83 -> 0.73 ms,
+    // C5 0.71 -> 0.65 ms), 1.5-3x BEHIND it below 20 (C4: 8 pixels per triangle).  $CRT_PACKET=0|1 overrides.
+    ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)
+    if (const char *k = std::getenv("CRT_PACKET"); k && *k)
+        ctx->packet_mode = *k == '1' ? 1 : 0;
     ctx->have_scene = true;
     return CRT_OK;
 }

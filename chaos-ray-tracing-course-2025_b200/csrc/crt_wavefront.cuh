@@ -136,6 +136,7 @@ __device__ __forceinline__ void write_ray(const DScene &S, const WfBuffers &b, i
 } // namespace crtdev
 #include "crt_trace.cuh"
 #include "crt_trace_light.cuh"
+#include "crt_trace_packet.cuh"
 namespace crtdev {
 
 // ------------------------------------------------------------------------------------------------ SHADE
@@ -417,7 +418,7 @@ inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, con
 // `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_light instead of k_wf_trace
 inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
                                     uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves,
-                                    int first_levels_only = 0, cudaEvent_t after_primary = nullptr) {
+                                    int first_levels_only = 0, cudaEvent_t after_primary = nullptr, bool packet_primary = false) {
     const int patches_x = (S.cam.width + 7) / 8, patches_y = (dp.rows + 3) / 4;
     const int P = patches_x * patches_y * 32;
     secondary = secondary && dp.max_ray_depth > 0;
@@ -433,7 +434,17 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     const int levels = first_levels_only > 0 ? min(first_levels_only, all_levels) : all_levels;
     const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? CRT_L_MINBLOCKS : 8);
     int n = 0;
-    if (traversal != CRT_TRAVERSAL_LITERAL) {
+    // primary level of the k-d walk as warp packets (crt_trace_packet.cuh): ray generation, root-box entry and the walk
+    // of a whole 8x4 patch in one kernel, no ray records
+    const bool packet = packet_primary && traversal == CRT_TRAVERSAL_KD;
+    if (packet) {
+        const int pb = min(w.sm_count * CRT_K_MINBLOCKS, (P / 32 + kTraceWarps - 1) / kTraceWarps);
+        if (stats)
+            k_wf_trace_packet<true><<<pb, kTraceBlock, 0, stream>>>(S, dp, w.b, counters);
+        else
+            k_wf_trace_packet<false><<<pb, kTraceBlock, 0, stream>>>(S, dp, w.b, counters);
+        ++n;
+    } else if (traversal != CRT_TRAVERSAL_LITERAL) {
         const int rb = min(w.sm_count * 16, (P + kRaygenBlock - 1) / kRaygenBlock);
         if (stats)
             k_wf_raygen<true><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters);
@@ -443,7 +454,9 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     }
     for (int level = 0; level < levels; ++level) {
         const int tb = level == 0 ? min(trace_blocks, (P + kTraceBlock - 1) / kTraceBlock) : trace_blocks;
-        if (traversal == CRT_TRAVERSAL_LITERAL)
+        if (packet && level == 0)
+            --n; // traced above
+        else if (traversal == CRT_TRAVERSAL_LITERAL)
             wavefront_launch_trace<CRT_TRAVERSAL_LITERAL>(w, S, dp, stats, level, tb, counters, stream, false);
         else
             wavefront_launch_trace<CRT_TRAVERSAL_KD>(w, S, dp, stats, level, tb, counters, stream, light_leaves);

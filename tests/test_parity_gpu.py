@@ -404,3 +404,31 @@ def test_images_below_half_a_bucket_stay_black_on_the_device_too(crt, ot, render
         assert same_bits(got, want["rgb"]) and np.array_equal(got8, want["rgb8"]) and stats["rays"] == want["stats"]["rays"]
     part, _, _ = renderer.render(crt.default_params(rank=1, world=2, band_rows=2))
     assert same_bits(part, want["rgb"][crt.Renderer.owned_rows(size[1], 1, 2, 2)])
+
+
+@pytest.mark.parametrize("rel", ["15-01-conclusion/scene1.crtscene", "11-01-refractive/scene8.crtscene", "12-01-textures/scene4.crtscene",
+                                 "14-01-acceleration-tree/scene1.crtscene"])
+def test_packet_primary_level_equals_the_per_lane_walk(crt, ot, rel, monkeypatch):
+    """$CRT_PACKET (read at upload): the primary level walked by warp packets (one 8x4 patch per warp, shared node stack)
+    and by the per-lane walk must give the same hits, the same frame bit for bit and the same ray counts, whole frames
+    and row bands, ragged sizes included"""
+    frames = {}
+    for packet in ("0", "1"):
+        monkeypatch.setenv("CRT_PACKET", packet)
+        r = crt.Renderer(0)
+        try:
+            for size in ((333, 187), (64, 36)):
+                scene, flat = load(crt, ot, rel, size)
+                r.upload(flat)
+                for pipeline in (crt.PIPELINE_WAVEFRONT, crt.PIPELINE_HYBRID):
+                    for kw in ({}, {"rank": 1, "world": 2, "band_rows": 8}):
+                        rgb, rgb8, stats = r.render(crt.default_params(pipeline=pipeline, max_ray_depth=5, collect_stats=1, **kw))
+                        key = (size, pipeline, tuple(kw.items()))
+                        if packet == "0":
+                            frames[key] = (rgb, rgb8, stats)
+                        else:
+                            want = frames[key]
+                            assert same_bits(rgb, want[0]) and np.array_equal(rgb8, want[1]), key
+                            assert stats["rays_by_depth"] == want[2]["rays_by_depth"] and stats["kernel_launches"] == want[2]["kernel_launches"] - 1
+        finally:
+            r.close()
