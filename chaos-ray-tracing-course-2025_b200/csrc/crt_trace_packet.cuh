@@ -13,7 +13,7 @@
 // local-memory array indexed by the warp-uniform stack pointer (one coalesced 256 B access per push / pop).
 // Triangles of a leaf are loaded once per warp (uniform) and tested by every lane that is active in the leaf.
 // Ray generation (Camera::generate_ray, crt_camera.cpp:7-35) and the root-box entry are done here too: no ray record
-// is written or read for the primary level.
+// is written or read for the primary level (only the slots of the rays that enter the box, for the level-0 shade).
 #pragma once
 
 namespace crtdev {
@@ -24,7 +24,8 @@ namespace crtdev {
 
 template <bool STATS>
 __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packet(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
-                                                                                  const __grid_constant__ WfBuffers b, Counters *__restrict__ counters) {
+                                                                                  const __grid_constant__ WfBuffers b, Counters *__restrict__ counters,
+                                                                                  float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
     __shared__ int node_stack[kTraceWarps][kStack];
     int *ns = node_stack[threadIdx.x >> 5];
     float2 ivl[kStack]; // my [tmin, tmax] in the cell of each pending node; tmax = -inf: that subtree is not mine to visit
@@ -34,13 +35,9 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
     const float kOut = -kInf;
     const V3 o = mk(S.cam.position[0], S.cam.position[1], S.cam.position[2]);
     Counters cn{};
-    for (;;) {
-        int patch = 0;
-        if (lane == 0)
-            patch = atomicAdd(&b.ctl->fetch[0], 1);
-        patch = __shfl_sync(full, patch, 0);
-        if (patch >= patches)
-            break;
+    // one patch per warp, handed out by the block scheduler (a shared cursor costs one atomic on a hot word per patch:
+    // 15 % of a 0.2 ms frame)
+    for (int patch = blockIdx.x * kTraceWarps + int(threadIdx.x >> 5); patch < patches; patch += gridDim.x * kTraceWarps) {
         const int slot = patch * 32 + int(lane);
         int x, ly;
         const bool have = slot_pixel(b, S, P, slot, x, ly);
@@ -56,11 +53,19 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
                 ++cn.node_tests;
             }
         }
-        if (!__any_sync(full, q.live)) { // the whole patch misses the root box
-            if (have)
-                b.hit[slot] = make_float2(kInf, __int_as_float(-1));
+        // a ray that misses the root box hits nothing: its pixel is final here; the others are queued for the level-0
+        // shade (slot only -- the shade stage regenerates the camera ray, as it does after k_wf_raygen)
+        if (have && !q.live)
+            write_pixel(S, rgb, rgb8, x, ly, mk(S.bg[0], S.bg[1], S.bg[2]));
+        const unsigned live_mask = __ballot_sync(full, q.live);
+        if (live_mask == 0u)
             continue;
-        }
+        int queue_base = 0;
+        if (lane == 0)
+            queue_base = atomicAdd(&b.ctl->count[0], __popc(live_mask));
+        queue_base = __shfl_sync(full, queue_base, 0);
+        if (q.live)
+            b.ray0_slot[queue_base + __popc(live_mask & ((1u << lane) - 1u))] = slot;
         const V3 d = r.d, inv = q.inv;
         float tmin = q.tmin, tmax = q.live ? q.tmax : kOut;
         unsigned long long best = kNoHitKey;
@@ -147,11 +152,8 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
                 tmin = f.x, tmax = f.y;
             }
         }
-        if (have) {
-            const float t = q.live ? __uint_as_float(unsigned(best >> 32)) : kInf;
-            const int tri = q.live ? int(unsigned(best & 0xffffffffull)) : -1;
-            b.hit[slot] = make_float2(t, __int_as_float(tri));
-        }
+        if (q.live)
+            b.hit[slot] = make_float2(__uint_as_float(unsigned(best >> 32)), __int_as_float(int(unsigned(best & 0xffffffffull))));
     }
     if (STATS)
         flush_counters(cn, counters);

@@ -83,9 +83,12 @@ __device__ __forceinline__ bool slot_pixel(const WfBuffers &b, const DScene &S, 
 // patch-major so neighbouring queue entries are neighbouring pixels); the others get their miss record right here.
 constexpr int kRaygenBlock = 256;
 
+__device__ __forceinline__ void write_pixel(const DScene &S, float *__restrict__ rgb, uint8_t *__restrict__ rgb8, int x, int ly, V3 c);
+
 template <bool STATS>
 __global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
-                                                             const __grid_constant__ WfBuffers b, Counters *__restrict__ counters) {
+                                                             const __grid_constant__ WfBuffers b, Counters *__restrict__ counters,
+                                                             float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
     const unsigned lane = threadIdx.x & 31u;
     Counters cn{};
     for (int first = blockIdx.x * kRaygenBlock + (threadIdx.x & ~31); first < b.P; first += gridDim.x * kRaygenBlock) {
@@ -117,7 +120,9 @@ __global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constan
             b.ray0_i[k] = make_float4(q.inv.x, q.inv.y, q.inv.z, q.tmax);
             b.ray0_slot[k] = slot;
         } else if (have) {
-            b.hit[slot] = make_float2(kInf, __int_as_float(-1));
+            // a ray that misses the root box hits nothing (crt_renderer.cpp:142-144): its pixel is final here, and the
+            // level-0 shade only visits the queued rays
+            write_pixel(S, rgb, rgb8, x, ly, mk(S.bg[0], S.bg[1], S.bg[2]));
         }
     }
     if (STATS)
@@ -152,20 +157,25 @@ constexpr int kShadeBlock = 128;
 
 __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
                                                           const __grid_constant__ WfBuffers b, int level, float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
-                                                          bool track_rows) {
+                                                          bool track_rows, bool queued0) {
+    // queued0 (level 0 after k_wf_raygen): visit the rays of the level-0 queue only; the pixels whose ray missed the root
+    // box were finished by the ray generation.  Otherwise (literal traversal) level 0 visits every pixel slot.
     WfCtl *ctl = b.ctl;
     const int start = level == 0 ? 0 : level_start(ctl, level);
-    const int total = level == 0 ? b.P : level_count(ctl, b.cap, level, start);
+    const int total = level == 0 ? (queued0 ? ctl->count[0] : b.P) : level_count(ctl, b.cap, level, start);
     const int next_start = level == 0 ? 0 : start + total;
     const unsigned lane = threadIdx.x & 31u;
     const V3 zero = mk(0.0f, 0.0f, 0.0f);
     // warp-uniform trip count: every lane of a warp runs the same iterations, so the collectives below are safe
     for (int first = (blockIdx.x * kShadeBlock + (threadIdx.x & ~31)); first < total; first += gridDim.x * kShadeBlock) {
-        const int i = first + int(lane);
+        int i = first + int(lane);
         int x = 0, ly = 0;
         bool have = i < total;
-        if (have && level == 0)
+        if (have && level == 0) {
+            if (queued0)
+                i = b.ray0_slot[i];
             have = slot_pixel(b, S, P, i, x, ly);
+        }
         const int node_id = level == 0 ? i : b.P + start + i;
         int kind = kTerminal, children = 0;
         V3 c = zero, albedo = zero, o0 = zero, d0 = zero, o1 = zero, d1 = zero;
@@ -437,19 +447,20 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     // primary level of the k-d walk as warp packets (crt_trace_packet.cuh): ray generation, root-box entry and the walk
     // of a whole 8x4 patch in one kernel, no ray records
     const bool packet = packet_primary && traversal == CRT_TRAVERSAL_KD;
+    const bool queued0 = traversal != CRT_TRAVERSAL_LITERAL; // k_wf_raygen / k_wf_trace_packet queue the rays that enter the root box
     if (packet) {
-        const int pb = min(w.sm_count * CRT_K_MINBLOCKS, (P / 32 + kTraceWarps - 1) / kTraceWarps);
+        const int pb = (P / 32 + kTraceWarps - 1) / kTraceWarps; // one patch per warp
         if (stats)
-            k_wf_trace_packet<true><<<pb, kTraceBlock, 0, stream>>>(S, dp, w.b, counters);
+            k_wf_trace_packet<true><<<pb, kTraceBlock, 0, stream>>>(S, dp, w.b, counters, rgb, rgb8);
         else
-            k_wf_trace_packet<false><<<pb, kTraceBlock, 0, stream>>>(S, dp, w.b, counters);
+            k_wf_trace_packet<false><<<pb, kTraceBlock, 0, stream>>>(S, dp, w.b, counters, rgb, rgb8);
         ++n;
     } else if (traversal != CRT_TRAVERSAL_LITERAL) {
         const int rb = min(w.sm_count * 16, (P + kRaygenBlock - 1) / kRaygenBlock);
         if (stats)
-            k_wf_raygen<true><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters);
+            k_wf_raygen<true><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters, rgb, rgb8);
         else
-            k_wf_raygen<false><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters);
+            k_wf_raygen<false><<<rb, kRaygenBlock, 0, stream>>>(S, dp, w.b, counters, rgb, rgb8);
         ++n;
     }
     for (int level = 0; level < levels; ++level) {
@@ -461,7 +472,7 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
         else
             wavefront_launch_trace<CRT_TRAVERSAL_KD>(w, S, dp, stats, level, tb, counters, stream, light_leaves);
         const int sb = level == 0 ? min(w.sm_count * 32, (P + kShadeBlock - 1) / kShadeBlock) : w.sm_count * 8;
-        k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8, level == 0 && after_primary != nullptr);
+        k_wf_shade<<<sb, kShadeBlock, 0, stream>>>(S, dp, w.b, level, rgb, rgb8, level == 0 && after_primary != nullptr, level == 0 && queued0);
         n += 2;
         // every pixel whose primary ray ends in a terminal surface is final now; the rest are rewritten by resolve
         if (level == 0 && after_primary && (e = cudaEventRecord(after_primary, stream)) != cudaSuccess)
