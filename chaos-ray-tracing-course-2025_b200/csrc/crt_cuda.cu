@@ -198,7 +198,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     const bool stats = params->collect_stats != 0;
     ctx->last_stats = stats;
     ctx->packet_primary = ctx->packet_mode >= 0 ? ctx->packet_mode == 1
-                                                : ctx->scene.n_triangles > 0 && double(W) * double(H) / double(ctx->scene.n_triangles) >= 256.0;
+                                                : ctx->scene.n_triangles > 0 && double(W) * double(H) / double(ctx->scene.n_triangles) >= 64.0;
     ctx->last_width = W;
     ctx->last_rows = dp.rows;
     ctx->last_launches = 0;
@@ -502,8 +502,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         ctx->light_leaves = std::strcmp(k, "light") == 0;
     // primary level as warp packets (crt_trace_packet.cuh): pays when a patch of 32 pixels sees few triangles -- the
     // rays of a warp then share their nodes and leaves.  Measured on B200 (tools/packet_sweep.py, profiles/
-    // r1z_packet_sweep.txt): ahead of the per-lane walk from ~130-500 pixels per triangle upwards (C3 0.83 -> 0.73 ms,
-    // C5 0.71 -> 0.65 ms), 1.5-3x BEHIND it below 20 (C4: 8 pixels per triangle).  $CRT_PACKET=0|1 overrides.
+    // r1z_packet_sweep.txt: height fields covering a quarter of the frame): 5-25 % ahead of the per-lane walk from ~60
+    // frame pixels per triangle upwards (C1 0.19 -> 0.17 ms, C3 0.82 -> 0.63 ms, C5 0.69 -> 0.63 ms), 1.3-3x BEHIND it
+    // below 20 (C4: 8 pixels per triangle).  Threshold 64; $CRT_PACKET=0|1 overrides.
     ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)
     if (const char *k = std::getenv("CRT_PACKET"); k && *k)
         ctx->packet_mode = *k == '1' ? 1 : 0;
