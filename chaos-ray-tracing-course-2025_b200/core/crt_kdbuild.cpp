@@ -202,30 +202,136 @@ struct Builder {
         dst.max_leaf = std::max(dst.max_leaf, src.max_leaf);
     }
 
-    // top of the tree: the two children of a large node are built concurrently
-    Subtree build_parallel(const Cell &cell, std::vector<uint32_t> &refs, int depth, int fork_levels) const {
+    // fn(chunk, begin, end) over `workers` contiguous ranges of [0, n), the last one on the calling thread
+    template <class Fn>
+    static void for_chunks(size_t n, int workers, Fn fn) {
+        std::vector<std::thread> pool;
+        for (int c = 0; c < workers; ++c) {
+            const size_t begin = n * size_t(c) / size_t(workers), end = n * size_t(c + 1) / size_t(workers);
+            if (c + 1 < workers)
+                pool.emplace_back([=] { fn(c, begin, end); });
+            else
+                fn(c, begin, end);
+        }
+        for (std::thread &t : pool)
+            t.join();
+    }
+
+    // find_split for the large nodes at the top of the tree, with the threads that have nothing else to do yet: the
+    // three axes are binned in one pass over the references, each worker counting its own range; the counts are
+    // integers, so the sums -- and with them the chosen plane -- are the serial ones
+    Split find_split_wide(const Cell &cell, const std::vector<uint32_t> &refs, int depth, int workers) const {
+        Split best;
+        const size_t n = refs.size();
+        if (n == 0 || depth >= p.max_depth)
+            return best;
+        const int K = p.bins;
+        std::vector<uint32_t> counts(size_t(workers) * 6 * size_t(K), 0); // [worker][axis][starts | ends][bin]
+        float scale[3];
+        for (int a = 0; a < 3; ++a)
+            scale[a] = float(K) / (cell.hi[a] - cell.lo[a]);
+        for_chunks(n, workers, [&](int c, size_t begin, size_t end) {
+            uint32_t *mine = counts.data() + size_t(c) * 6 * size_t(K);
+            for (size_t i = begin; i < end; ++i) {
+                const TriBox &b = boxes[refs[i]];
+                for (int a = 0; a < 3; ++a) {
+                    const float clo = cell.lo[a], chi = cell.hi[a];
+                    if (!(chi - clo > 0.0f))
+                        continue;
+                    const int st = std::clamp(int((std::max(b.lo[a], clo) - clo) * scale[a]), 0, K - 1);
+                    const int en = std::clamp(int((std::min(b.hi[a], chi) - clo) * scale[a]), 0, K - 1);
+                    ++mine[size_t(2 * a) * size_t(K) + size_t(st)], ++mine[size_t(2 * a + 1) * size_t(K) + size_t(en)];
+                }
+            }
+        });
+        for (int c = 1; c < workers; ++c)
+            for (size_t k = 0; k < 6 * size_t(K); ++k)
+                counts[k] += counts[size_t(c) * 6 * size_t(K) + k];
+        for (int axis = 0; axis < 3; ++axis) {
+            const float clo = cell.lo[axis], chi = cell.hi[axis], da = chi - clo;
+            if (!(da > 0.0f))
+                continue;
+            const uint32_t *starts = counts.data() + size_t(2 * axis) * size_t(K), *ends = starts + K;
+            size_t nl = 0, ended = 0;
+            for (int k = 1; k < K; ++k) { // as in sweep_binned
+                nl += starts[k - 1];
+                ended += ends[k - 1];
+                const size_t nr = n - ended;
+                const float plane = clo + da * (float(k) / float(K));
+                if (!(plane > clo && plane < chi))
+                    continue;
+                const float c = split_cost(cell, axis, plane, nl, nr);
+                if (c < best.cost && !(nl == n && nr == n))
+                    best = Split{ axis, plane, c };
+            }
+        }
+        if (best.valid() && best.cost >= leaf_cost(n) && n <= 64)
+            best = Split{};
+        return best;
+    }
+
+    // partition() with every worker filling its own stretch of the two lists: same lists, same order
+    void partition_wide(const std::vector<uint32_t> &refs, const Split &s, std::vector<uint32_t> &left, std::vector<uint32_t> &right, int workers) const {
+        const auto sides = [&](uint32_t t, bool &l, bool &r) {
+            const float lo = boxes[t].lo[s.axis], hi = boxes[t].hi[s.axis];
+            const bool in_plane = lo == s.plane && hi == s.plane;
+            l = lo < s.plane || in_plane, r = hi > s.plane || in_plane;
+        };
+        std::vector<size_t> nl(size_t(workers) + 1, 0), nr(size_t(workers) + 1, 0);
+        for_chunks(refs.size(), workers, [&](int c, size_t begin, size_t end) {
+            size_t a = 0, b = 0;
+            for (size_t i = begin; i < end; ++i) {
+                bool l, r;
+                sides(refs[i], l, r);
+                a += l, b += r;
+            }
+            nl[size_t(c) + 1] = a, nr[size_t(c) + 1] = b;
+        });
+        for (int c = 0; c < workers; ++c)
+            nl[size_t(c) + 1] += nl[size_t(c)], nr[size_t(c) + 1] += nr[size_t(c)];
+        left.resize(nl[size_t(workers)]), right.resize(nr[size_t(workers)]);
+        for_chunks(refs.size(), workers, [&](int c, size_t begin, size_t end) {
+            size_t a = nl[size_t(c)], b = nr[size_t(c)];
+            for (size_t i = begin; i < end; ++i) {
+                bool l, r;
+                sides(refs[i], l, r);
+                if (l)
+                    left[a++] = refs[i];
+                if (r)
+                    right[b++] = refs[i];
+            }
+        });
+    }
+
+    // top of the tree: the two children of a large node are built concurrently, and while there are fewer such nodes
+    // than threads (`workers` of them are free at this node) the node's own binning and partition are spread out too
+    Subtree build_parallel(const Cell &cell, std::vector<uint32_t> &refs, int depth, int fork_levels, int workers) const {
         Subtree out;
         if (fork_levels <= 0 || refs.size() < 16384) {
             build_serial(out, cell, refs, depth);
             return out;
         }
-        const Split s = find_split(cell, refs, depth);
+        const bool wide = workers > 1 && refs.size() > size_t(p.exact_below);
+        const Split s = wide ? find_split_wide(cell, refs, depth, workers) : find_split(cell, refs, depth);
         if (!s.valid()) {
             build_serial(out, cell, refs, depth);
             return out;
         }
         std::vector<uint32_t> left, right;
-        partition(refs, s, left, right);
+        if (wide)
+            partition_wide(refs, s, left, right, workers);
+        else
+            partition(refs, s, left, right);
         std::vector<uint32_t>().swap(refs);
         Cell cl = cell, cr = cell;
         cl.hi[s.axis] = s.plane, cr.lo[s.axis] = s.plane;
         Subtree sub_l, sub_r;
         std::thread worker([&] {
             if (!left.empty())
-                sub_l = build_parallel(cl, left, depth + 1, fork_levels - 1);
+                sub_l = build_parallel(cl, left, depth + 1, fork_levels - 1, (workers + 1) / 2);
         });
         if (!right.empty())
-            sub_r = build_parallel(cr, right, depth + 1, fork_levels - 1);
+            sub_r = build_parallel(cr, right, depth + 1, fork_levels - 1, std::max(1, workers / 2));
         worker.join();
         out.nodes.push_back(crt_kd_node{ s.plane, -1, -1, s.axis });
         out.max_depth = depth;
@@ -277,7 +383,7 @@ KdBuildStats build_sah_tree(const crt_float4 *tri_verts, size_t n_triangles, con
     int fork_levels = 0;
     while ((1 << fork_levels) < std::max(1, threads) * 2 && fork_levels < 8)
         ++fork_levels;
-    Subtree tree = builder.build_parallel(root, all, 0, threads > 1 ? fork_levels : 0);
+    Subtree tree = builder.build_parallel(root, all, 0, threads > 1 ? fork_levels : 0, std::max(1, threads));
     nodes = std::move(tree.nodes);
     refs = std::move(tree.refs);
     KdBuildStats stats;
