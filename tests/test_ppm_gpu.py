@@ -55,15 +55,24 @@ def test_cli_writes_the_same_file_with_either_encoder(crt, ot, tmp_path):
     text, root = _scene(ot, 320, 180, "15-01-conclusion/scene1.crtscene")
     scene.write_text(text)
     outs = {}
-    for mode in ("device", "host", "group"):  # group: CRT_DEVICES lists several contexts (here the same GPU twice)
+    # group: CRT_DEVICES lists several contexts (here the same GPU twice); literal: the verification traversal, the only
+    # mode in which the CLI builds and uploads the reference's tree; lane / packet: both primary-level kernels
+    for mode in ("device", "host", "group", "literal", "lane", "packet"):
         out = tmp_path / f"{mode}.ppm"
         env = dict(os.environ, CRT_PPM="host" if mode == "host" else "device")
         if mode == "group":
             env["CRT_DEVICES"] = "0,0"
+        if mode == "literal":
+            env["CRT_TRAVERSAL"] = "0"
+        if mode in ("lane", "packet"):
+            env["CRT_PACKET"] = "1" if mode == "packet" else "0"
         proc = subprocess.run([cli, str(scene), str(out)], env=env, capture_output=True, text=True, timeout=120)
         assert proc.returncode == 0 and proc.stdout.startswith("Execution time: "), proc.stderr
         outs[mode] = out.read_bytes()
-    assert outs["device"] == outs["host"] == outs["group"] and outs["device"].startswith(b"P3\n320 180\n255\n")
+    assert outs["device"] == outs["host"] == outs["group"] == outs["lane"] == outs["packet"] and outs["device"].startswith(b"P3\n320 180\n255\n")
+    a = np.array(outs["device"].split(b"\n", 3)[3].split(), dtype=np.int64)
+    b = np.array(outs["literal"].split(b"\n", 3)[3].split(), dtype=np.int64)
+    assert a.shape == b.shape and (np.abs(a - b).reshape(-1, 3).max(axis=1) <= 1).mean() >= 0.999
     if ot.have_reference_build():
         ref = tmp_path / "ref.ppm"
         subprocess.run([os.path.join(ot.REF_DIR, "crt_renderer_ref"), str(scene), str(ref)], check=True, capture_output=True, timeout=300)

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Render a few frames of a bench workload through the C ABI (no torch): the short command ncu wraps.
-usage: python tools/render_frames.py <workload> [frames] [pipeline auto|mega|wavefront] [traversal kd|literal] [stats 0|1]"""
+usage: python tools/render_frames.py <workload> [frames] [pipeline auto|mega|wavefront] [traversal kd|literal] [stats 0|1] [WxH]"""
 import os
 import sys
 
@@ -17,7 +17,8 @@ traversal = sys.argv[4] if len(sys.argv) > 4 else "kd"
 stats = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 crt = entry.load_package()
 desc, W, H, depth, _ = bench.WORKLOADS[workload]
-text, root = bench.scene_text(workload)
+size = tuple(int(v) for v in sys.argv[6].split("x")) if len(sys.argv) > 6 else None  # e.g. 540x540: a smaller frame for ncu
+text, root = bench.scene_text(workload, size)
 scene = crt.Scene.load_json(text, root)
 r = crt.Renderer(0)
 flat = r.upload(scene.flatten(reference_tree=traversal == "literal"))
