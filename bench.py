@@ -168,6 +168,7 @@ def run_ours(args):
     device = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version / warning lines stay off stdout: ONE JSON line there
         dist.init_process_group("nccl", device_id=device)
 
     desc, W, H, depth, _ = WORKLOADS[args.workload]
