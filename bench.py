@@ -177,7 +177,7 @@ def run_reference_arm(args):
     ref = reference_sample(args.workload, args.steps, args.warmup)
     desc = WORKLOADS[args.workload][0]
     line = {"impl": "reference", "metric": "Mrays/s (primary+secondary)", "value": ref["value"], "unit": "Mrays/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ref["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ref["ms_per_step"], "higher_is_better": True, "scaling": "weak" if args.partition == "frames" else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "sample": ref["sample"]},
             "cpu_baseline": {"value": ref["value"], "unit": "Mrays/s", "cores": ref["cores"], "kind": ref["kind"], "sample": ref["sample"]},
@@ -408,7 +408,7 @@ def run_ours(args):
             cpu = {"value": None, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference", "sample": f"failed: {exc}"}
 
     line = {"metric": "Mrays/s (primary+secondary)", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if frame_parallel else "strong", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if (frame_parallel or args.partition == "frames") else "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "traversal": "kd", "pipeline": args.pipeline, "partition": ("whole frames per rank (frame k -> rank k % N), no exchange" if frame_parallel else f"row bands of {band_rows}, " + ("pushed into rank 0's frame by peer stores over NVLink + 1-element all-reduce as the barrier" if args.gather == "peer" else "NCCL gather of u8 rgb to rank 0")) if world > 1 else "single GPU",
                        "l2": "256 MiB flush between timed steps", "rays_per_step": job_rays_per_step, "scene_load_s": t_load, "scene_upload_s": t_upload,

@@ -407,6 +407,54 @@ int crt_cuda_set_stream(crt_cuda_ctx *ctx, void *stream) {
     return CRT_OK;
 }
 
+// The walk tree in the device's 8-byte records (crt_device.cuh: kd_node_at).  Nodes are re-numbered so that the children
+// of a node sit side by side (a, then b; an absent child takes no slot): the root stays node 0, a node's children are
+// numbered when the node is reached, and child a's subtree is laid out before child b's, which keeps the pre-order
+// locality of the builder's numbering along the a-chains.  Returns NULL, or what is wrong with the tree.
+static const char *pack_walk_nodes(const crt_kd_node *src, int n, int2 *dst) {
+    if (n > kNode8MaxNodes)
+        return "walk tree has more nodes than the 8-byte device node can address (2^28)";
+    std::vector<std::pair<int, int>> todo; // {builder's index, device index}
+    todo.reserve(128);
+    todo.push_back({ 0, 0 });
+    int next = 1;
+    while (!todo.empty()) {
+        const auto [from, to] = todo.back();
+        todo.pop_back();
+        const crt_kd_node &k = src[from];
+        if (k.axis == 3) {
+            if (k.b < 0 || k.b >= kNode8MaxCount)
+                return "walk tree leaf with a broken triangle count";
+            dst[to] = make_int2(k.a, int(3u | (uint32_t(k.b) << 2)));
+            continue;
+        }
+        if (k.axis < 0 || k.axis > 2 || k.a >= n || k.b >= n)
+            return "walk tree node with a broken axis or child index";
+        const int has_a = k.a >= 0, has_b = k.b >= 0;
+        const int child = next;
+        next += has_a + has_b;
+        if (next > n)
+            return "walk tree is not a tree (nodes reachable twice do not unfold into n records)";
+        int split_bits;
+        std::memcpy(&split_bits, &k.split, 4);
+        dst[to] = make_int2(split_bits, int(uint32_t(k.axis) | uint32_t(has_a) << 2 | uint32_t(has_b) << 3 | uint32_t(child) << 4));
+        if (has_b)
+            todo.push_back({ k.b, child + has_a });
+        if (has_a)
+            todo.push_back({ k.a, child });
+    }
+    for (int i = next; i < n; ++i) // nodes nothing points to (none in the trees of core/): harmless, keep them inert
+        dst[i] = make_int2(0, 3);
+    return nullptr;
+}
+
+int crt_cuda_pack_walk_tree(const crt_kd_node *nodes, int32_t n_nodes, uint64_t *out) {
+    if (!nodes || !out || n_nodes < 1)
+        return CRT_ERR_INVALID;
+    static_assert(sizeof(int2) == sizeof(uint64_t), "8-byte node record");
+    return pack_walk_nodes(nodes, n_nodes, reinterpret_cast<int2 *>(out)) ? CRT_ERR_INVALID : CRT_OK;
+}
+
 int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     if (!ctx)
         return CRT_ERR_INVALID;
@@ -434,7 +482,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         { s->vert_normal, size_t(s->n_vertices) * sizeof(crt_float4), 0 },
         { s->vert_uv, size_t(s->n_vertices) * 2 * sizeof(float), 0 },
         { s->box_nodes, size_t(s->n_nodes) * sizeof(crt_box_node), 0 },
-        { s->fast_nodes, size_t(s->n_fast_nodes) * sizeof(crt_kd_node), 0 },
+        { s->fast_nodes, size_t(s->n_fast_nodes) * sizeof(KdNodeRec), 0 }, // CRT_NODE8: packed below, not copied
         { s->refs, size_t(s->n_refs) * sizeof(uint32_t), 0 },
         { s->lights, size_t(s->n_lights) * sizeof(crt_float4), 0 },
         { s->materials, size_t(s->n_materials) * sizeof(crt_material), 0 },
@@ -464,8 +512,12 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // make sure an earlier frame is not still reading the arena we are about to overwrite
     CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
     for (const Part &p : parts)
-        if (p.bytes)
+        if (p.bytes && !(CRT_NODE8 && &p == &parts[5]))
             std::memcpy(ctx->h_arena + p.offset, p.src, p.bytes);
+#if CRT_NODE8
+    if (const char *why = pack_walk_nodes(s->fast_nodes, s->n_fast_nodes, reinterpret_cast<int2 *>(ctx->h_arena + parts[5].offset)))
+        return fail(ctx, CRT_ERR_INVALID, why);
+#endif
     CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena, ctx->h_arena, total, cudaMemcpyHostToDevice, ctx->stream));
 
     DScene &d = ctx->scene;
@@ -481,7 +533,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     d.vert_normal = reinterpret_cast<const float4 *>(ctx->d_arena + parts[2].offset);
     d.vert_uv = reinterpret_cast<const float2 *>(ctx->d_arena + parts[3].offset);
     d.box_nodes = reinterpret_cast<const float4 *>(ctx->d_arena + parts[4].offset);
-    d.kd_nodes = reinterpret_cast<const int4 *>(ctx->d_arena + parts[5].offset);
+    d.kd_nodes = reinterpret_cast<const KdNodeRec *>(ctx->d_arena + parts[5].offset);
     d.refs = reinterpret_cast<const uint32_t *>(ctx->d_arena + parts[6].offset);
     d.lights = reinterpret_cast<const float4 *>(ctx->d_arena + parts[7].offset);
     d.materials = reinterpret_cast<const int4 *>(ctx->d_arena + parts[8].offset);

@@ -16,6 +16,23 @@
 namespace crtdev {
 
 // ------------------------------------------------------------------------------------------------ scene view
+// Walk-tree node as the kernels read it.  CRT_NODE8 = 1: 8 bytes {split | first, axis:2 has_a:1 has_b:1 child:28} --
+// crt_cuda_upload_scene re-numbers the nodes so that the children of a node are neighbours (child a at `child`, child b
+// right after it), which makes one index do for both; a leaf is {first reference, axis = 3 | count << 2}.  Half the
+// bytes of the 16-byte crt_kd_node: four nodes per 32-byte sector, siblings in the same sector, and a C4 walk tree of
+// 24 MB instead of 49 MB in L2.  kd_node_at() hands the kernels the {split, a, b, axis} / {0, first, count, 3} int4
+// they were written against.
+#ifndef CRT_NODE8
+#define CRT_NODE8 1
+#endif
+#if CRT_NODE8
+typedef int2 KdNodeRec;
+#else
+typedef int4 KdNodeRec;
+#endif
+constexpr int kNode8MaxNodes = 1 << 28; // child index field
+constexpr int kNode8MaxCount = 1 << 29; // leaf count field (a leaf is marked by the low two bits = 3)
+
 struct DScene {
     crt_camera cam;
     float bg[3];
@@ -27,7 +44,7 @@ struct DScene {
     const float4 *__restrict__ vert_normal; // 1 per vertex
     const float2 *__restrict__ vert_uv;     // 1 per vertex
     const float4 *__restrict__ box_nodes;   // 2 per node
-    const int4 *__restrict__ kd_nodes;      // 1 per node of the walk tree (crt_flat_scene.fast_nodes)
+    const KdNodeRec *__restrict__ kd_nodes; // 1 per node of the walk tree (crt_flat_scene.fast_nodes), see kd_node_at
     const uint32_t *__restrict__ kd_refs;   // its leaf lists (crt_flat_scene.fast_refs)
     const uint32_t *__restrict__ refs;      // leaf lists of the reference tree (box_nodes)
     const float4 *__restrict__ lights;
@@ -35,6 +52,19 @@ struct DScene {
     const float4 *__restrict__ textures; // 3 float4 per texture (crt_texture is 48 B)
     const float4 *__restrict__ texels;
 };
+
+__device__ __forceinline__ int4 kd_node_at(const DScene &S, int i) {
+#if CRT_NODE8
+    const int2 r = __ldg(&S.kd_nodes[i]);
+    const int axis = r.y & 3;
+    const unsigned u = unsigned(r.y);
+    const int has_a = int(u >> 2) & 1, has_b = int(u >> 3) & 1, child = int(u >> 4);
+    const bool leaf = axis == 3;
+    return make_int4(r.x, leaf ? r.x : (has_a ? child : -1), leaf ? int(u >> 2) : (has_b ? child + has_a : -1), axis);
+#else
+    return __ldg(&S.kd_nodes[i]);
+#endif
+}
 
 struct DParams {
     uint32_t max_ray_depth, gi_rays;
@@ -382,7 +412,7 @@ struct KdWalker {
     template <bool STATS>
     __device__ __forceinline__ int4 descend(const DScene &S, Counters *cn) {
         for (;;) {
-            const int4 n = __ldg(&S.kd_nodes[node]);
+            const int4 n = kd_node_at(S, node);
             if (n.w == 3)
                 return n;
             const int axis = n.w;

@@ -387,7 +387,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
         const bool walking = my >= 0 && !w.done();
         int4 n = make_int4(0, 0, 0, 0);
         if (walking)
-            n = __ldg(&S.kd_nodes[w.node]);
+            n = kd_node_at(S, w.node);
         const unsigned walkers = __ballot_sync(full, walking);
         const unsigned leaves = __ballot_sync(full, leaf_count > 0);
         // ---- b. the oldest candidates load their triangles: a full batch, or whatever is queued once too few lanes
@@ -471,7 +471,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
                 if (k > 0) {
                     if (w.done() || leaf_count > 0)
                         break;
-                    n = __ldg(&S.kd_nodes[w.node]);
+                    n = kd_node_at(S, w.node);
                 }
                 if (w.step<STATS>(ws, spill, lane, n, best_t, cn))
                     leaf_first = n.y, leaf_count = n.z, w.node = -1;

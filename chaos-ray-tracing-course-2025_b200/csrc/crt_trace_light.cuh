@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                     break;
                 bool need_pop = w.prune_at_visit(best_t);
                 if (!need_pop) {
-                    const int4 n = __ldg(&S.kd_nodes[w.node]);
+                    const int4 n = kd_node_at(S, w.node);
                     if (n.w == 3) {
                         if (p1_count == 0) {
                             if (p0_count == 0)

@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
             const bool act = tmax != kOut && !(tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best_t);
             bool descend = false;
             if (__any_sync(full, act)) {
-                const int4 n = __ldg(&S.kd_nodes[node]);
+                const int4 n = kd_node_at(S, node);
                 if (STATS && act && node != 0)
                     ++cn.node_tests;
                 if (n.w == 3) {

@@ -198,6 +198,13 @@ int crt_cuda_set_stream(crt_cuda_ctx *ctx, void *stream);
 
 /* cudaMemcpyAsync of every array from (internally pinned) staging; replaces the implicit "scene is in RAM" */
 int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *scene);
+/* Host-only helper (no device needed), exposed for tests and tools: the walk tree as crt_cuda_upload_scene lays it out
+ * in device memory -- 8 bytes per node instead of crt_kd_node's 16, nodes re-numbered so that the two children of a
+ * node are neighbours.  out: n_nodes records.  Inner node: low word = split (float bits), high word = axis (bits 0-1)
+ * | has_a << 2 | has_b << 3 | index of the first present child << 4 (child b follows child a).  Leaf: low word = first
+ * reference, high word = 3 | count << 2.  The root stays node 0.  CRT_ERR_INVALID for a broken tree (shared nodes
+ * that do not unfold into n_nodes records, a bad axis, an index out of range, more than 2^28 nodes). */
+int crt_cuda_pack_walk_tree(const crt_kd_node *nodes, int32_t n_nodes, uint64_t *out);
 /* cheap per-frame update (animation): only the 72 B camera block */
 int crt_cuda_set_camera(crt_cuda_ctx *ctx, const crt_camera *camera);
 

@@ -271,3 +271,58 @@ def test_flatten_without_the_reference_tree(crt, ot, rel):
         assert np.array_equal(c[key], b[key]), key
     assert later.n_nodes == full.n_nodes and later.max_depth == full.max_depth
     assert np.array_equal(lean.arrays()["fast_nodes"], b["fast_nodes"])  # the first view still reads the same arrays
+
+
+def _pack(crt, nodes):
+    nodes = np.ascontiguousarray(nodes, dtype=np.int32)
+    out = np.zeros(len(nodes), dtype=np.uint64)
+    rc = crt.lib.crt_cuda_pack_walk_tree(nodes.ctypes.data, len(nodes), out.ctypes.data)
+    return rc, out
+
+
+@needs_scenes
+@pytest.mark.parametrize("walk_tree", ["sah", "reference"])
+@pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "15-01-conclusion/scene2.crtscene", "14-01-acceleration-tree/scene0.crtscene",
+                                 "12-01-textures/scene4.crtscene"])
+def test_device_node_records_hold_the_same_tree(crt, ot, rel, walk_tree, monkeypatch):
+    """crt_cuda_pack_walk_tree (what crt_cuda_upload_scene puts in device memory): 8 bytes per node, children side by
+    side.  Walked together with the 16-byte tree it came from, it has the same planes, axes, absent children and leaf
+    lists; every node is used exactly once; the root is node 0."""
+    if walk_tree == "reference":
+        monkeypatch.setenv("CRT_WALK_TREE", "reference")
+    flat = crt.Scene.load_file(ot.scene_file(rel)).flatten(reference_tree=walk_tree == "reference")
+    fast = flat.arrays()["fast_nodes"]
+    rc, packed = _pack(crt, fast)
+    assert rc == 0
+    lo, hi = (packed & 0xFFFFFFFF).astype(np.uint32), (packed >> 32).astype(np.uint32)
+    used = np.zeros(len(fast), dtype=np.int32)
+    todo = [(0, 0)]
+    while todo:
+        old, new = todo.pop()
+        used[new] += 1
+        split_bits, a, b, axis = (int(v) for v in fast[old])
+        assert int(hi[new] & 3) == axis
+        if axis == 3:
+            assert int(lo[new]) == a and int(hi[new] >> 2) == b, "leaf: first reference and count"
+            continue
+        assert int(lo[new]) == split_bits & 0xFFFFFFFF, "split plane bit for bit"
+        has_a, has_b, child = int(hi[new] >> 2) & 1, int(hi[new] >> 3) & 1, int(hi[new] >> 4)
+        assert has_a == (a >= 0) and has_b == (b >= 0)
+        assert not (has_a or has_b) or 0 < child and child + has_a + has_b <= len(fast)
+        if has_a:
+            todo.append((a, child))
+        if has_b:
+            todo.append((b, child + has_a))
+    assert (used == 1).all(), "a permutation of the nodes"
+
+
+def test_device_node_packing_refuses_broken_trees(crt):
+    leaf = [0, 0, 1, 3]
+    assert _pack(crt, [[0, 1, 2, 0], leaf, leaf])[0] == 0
+    assert _pack(crt, [[0, 1, 1, 0], leaf])[0] == crt.ERR_INVALID  # a node reachable twice: does not unfold into n records
+    assert _pack(crt, [[0, 1, 2, 5], leaf, leaf])[0] == crt.ERR_INVALID  # axis out of range
+    assert _pack(crt, [[0, 1, 7, 1], leaf, leaf])[0] == crt.ERR_INVALID  # child index out of range
+    assert _pack(crt, [[0, 0, -1, 3]])[0] == crt.ERR_INVALID            # leaf with a negative count
+    assert crt.lib.crt_cuda_pack_walk_tree(None, 1, None) == crt.ERR_INVALID
+    rc, one = _pack(crt, [[7, -1, 2, 1], leaf, leaf])  # child a absent: b takes the first slot
+    assert rc == 0 and int(one[0] >> 32) == (1 | 0 << 2 | 1 << 3 | 1 << 4)
