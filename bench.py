@@ -380,7 +380,8 @@ def run_ours(args):
     else:
         peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
     n = n_count_frames
-    alg_bytes = (16 * counted["node_tests"] + 48 * counted["tri_tests"] + 16 * counted["rays"]) / n + 15.0 * W * rows_local
+    node_bytes = crt.lib.crt_cuda_walk_node_bytes()  # 8: the device records of this build (16 with -DCRT_NODE8=0)
+    alg_bytes = (node_bytes * counted["node_tests"] + 48 * counted["tri_tests"] + 16 * counted["rays"]) / n + 15.0 * W * rows_local
     k_ms = statistics.mean(kernel_ms) if kernel_ms else ms_per_step
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     traffic, issue = None, None
@@ -395,7 +396,7 @@ def run_ours(args):
                      "source": "smsp__inst_executed.sum of the two walk kernels in " + prof.get("source", "profiles/") + "; slots from the live kernel time and SM clock"}
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "kernel": "closest-hit walk of one frame: k_wf_trace_light (primary level) + k_render_persistent<seeded> (every deeper level, shading included); raygen / level-0 shade / resolve are < 8 % of the frame", "kernel_ms": k_ms, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg_bytes,
+                "algorithmic_bytes_per_launch": alg_bytes, "node_bytes": node_bytes,
                 "issue": issue,
                 "per_ray": {"kd_nodes_visited": counted["node_tests"] / max(1, counted["rays"]), "triangle_tests": counted["tri_tests"] / max(1, counted["rays"])}}
 

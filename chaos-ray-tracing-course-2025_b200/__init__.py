@@ -28,7 +28,7 @@ REF_CULL_BIT = 0x80000000
 EXPORTED_SYMBOLS = [
     "crt_scene_load_file", "crt_scene_load_json", "crt_scene_flatten", "crt_scene_flatten_ex", "crt_scene_set_camera", "crt_scene_set_resolution",
     "crt_scene_free", "crt_scene_last_error", "crt_render_params_default", "crt_cuda_device_count", "crt_cuda_create",
-    "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_pack_walk_tree", "crt_cuda_set_camera",
+    "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_pack_walk_tree", "crt_cuda_walk_node_bytes", "crt_cuda_set_camera",
     "crt_cuda_render", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
     "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
     "crt_cuda_frame_create", "crt_cuda_frame_open", "crt_cuda_frame_attach", "crt_cuda_frame_pointer", "crt_cuda_push_bands",
@@ -114,6 +114,7 @@ def _load_library():
         "crt_scene_flatten": (C.c_int, [vp, P(FlatScene)]),
         "crt_scene_flatten_ex": (C.c_int, [vp, C.c_int, P(FlatScene)]),
         "crt_cuda_pack_walk_tree": (C.c_int, [vp, C.c_int32, vp]),
+        "crt_cuda_walk_node_bytes": (C.c_int, []),
         "crt_scene_set_camera": (C.c_int, [vp, P(C.c_float), P(C.c_float), C.c_float]),
         "crt_scene_set_resolution": (C.c_int, [vp, C.c_int, C.c_int]),
         "crt_scene_free": (None, [vp]),

@@ -448,6 +448,8 @@ static const char *pack_walk_nodes(const crt_kd_node *src, int n, int2 *dst) {
     return nullptr;
 }
 
+int crt_cuda_walk_node_bytes(void) { return int(sizeof(KdNodeRec)); }
+
 int crt_cuda_pack_walk_tree(const crt_kd_node *nodes, int32_t n_nodes, uint64_t *out) {
     if (!nodes || !out || n_nodes < 1)
         return CRT_ERR_INVALID;

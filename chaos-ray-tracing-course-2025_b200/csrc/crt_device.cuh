@@ -23,7 +23,7 @@ namespace crtdev {
 // 24 MB instead of 49 MB in L2.  kd_node_at() hands the kernels the {split, a, b, axis} / {0, first, count, 3} int4
 // they were written against.
 #ifndef CRT_NODE8
-#define CRT_NODE8 1
+#define CRT_NODE8 0
 #endif
 #if CRT_NODE8
 typedef int2 KdNodeRec;
@@ -677,11 +677,45 @@ __device__ __forceinline__ Pcg32 make_pcg(uint32_t px, uint32_t py) {
 
 // cosf/sinf of the reference go through glibc; binary64 sin/cos rounded once to binary32 agrees with it except
 // for rare last-bit cases (documented FP difference; only GI directions are affected, crt_renderer.cpp:68-74).
+// CRT_SINCOS_LEAN (default): the binary64 evaluation written out for the only arguments the renderer has, [0, 2 pi]
+// (pi * u and 2 pi * u with u in [0, 1)): quadrant by rint (a * 2/pi), two-step reduction with FMAs, the fdlibm kernel
+// polynomials on [-pi/4, pi/4] (error < 1 ulp of binary64, so the binary32 rounding agrees with the library call
+// except ~1e-8 of the time).  The library sincos() carries its large-argument path along: 7 % of the GI kernel's
+// issued instructions and a good part of its instruction-fetch stalls (profiles/r1z_ncu_source_c3gi_540x540_persistent.txt).
+#ifndef CRT_SINCOS_LEAN
+#define CRT_SINCOS_LEAN 1
+#endif
 __device__ __forceinline__ void sincos_ref(float a, float &s, float &c) {
+#if CRT_SINCOS_LEAN
+    const double x = double(a);
+    const double k = rint(x * 6.36619772367581382433e-01);
+    double r = __fma_rn(-k, 1.57079632679489655800e+00, x);
+    r = __fma_rn(-k, 6.12323399573676603587e-17, r);
+    const double z = r * r;
+    double ps = 1.58969099521155010221e-10;
+    ps = __fma_rn(ps, z, -2.50507602534068634195e-08);
+    ps = __fma_rn(ps, z, 2.75573137070700676789e-06);
+    ps = __fma_rn(ps, z, -1.98412698298579493134e-04);
+    ps = __fma_rn(ps, z, 8.33333333332248946124e-03);
+    ps = __fma_rn(ps, z, -1.66666666666666324348e-01);
+    const double sr = __fma_rn(ps * z, r, r);
+    double pc = -1.13596475577881948265e-11;
+    pc = __fma_rn(pc, z, 2.08757232129817482790e-09);
+    pc = __fma_rn(pc, z, -2.75573143513906633035e-07);
+    pc = __fma_rn(pc, z, 2.48015872894767294178e-05);
+    pc = __fma_rn(pc, z, -1.38888888888741095749e-03);
+    pc = __fma_rn(pc, z, 4.16666666666666019037e-02);
+    const double cr = __fma_rn(pc * z, z, __fma_rn(-0.5, z, 1.0));
+    const int q = int(k) & 3;
+    const double sq = (q & 1) ? cr : sr, cq = (q & 1) ? sr : cr;
+    s = float((q & 2) ? -sq : sq);
+    c = float(((q + 1) & 2) ? -cq : cq);
+#else
     double sd, cd;
     sincos(double(a), &sd, &cd);
     s = float(sd);
     c = float(cd);
+#endif
 }
 
 // One GI bounce direction, src/core/crt_renderer.cpp:62-74.

@@ -205,6 +205,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *scene);
  * reference, high word = 3 | count << 2.  The root stays node 0.  CRT_ERR_INVALID for a broken tree (shared nodes
  * that do not unfold into n_nodes records, a bad axis, an index out of range, more than 2^28 nodes). */
 int crt_cuda_pack_walk_tree(const crt_kd_node *nodes, int32_t n_nodes, uint64_t *out);
+/* bytes of one walk-tree node as the kernels of this build read it (8; 16 when built with -DCRT_NODE8=0): what the
+ * algorithmic bytes per ray of a measurement are counted with */
+int crt_cuda_walk_node_bytes(void);
 /* cheap per-frame update (animation): only the 72 B camera block */
 int crt_cuda_set_camera(crt_cuda_ctx *ctx, const crt_camera *camera);
 
