@@ -13,6 +13,7 @@
 #include "crt_persistent.cuh"
 #include "crt_ppm.cuh"
 #include "crt_push.cuh"
+#include "crt_gi.h"
 
 using namespace crtdev;
 
@@ -163,10 +164,9 @@ template <bool SEEDED, bool SHADOWS>
 void launch_persistent(crt_cuda_ctx *ctx, const DParams &dp, bool stats, bool gi, int blocks, int patches_x, int n_slots) {
 #define CRT_LAUNCH_P(ST, G) \
     k_render_persistent<ST, G, SEEDED, SHADOWS><<<blocks, kTraceBlock, 0, ctx->stream>>>(ctx->scene, dp, ctx->d_pctl, patches_x, n_slots, ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, ctx->wf.b)
-    if (gi && stats)
-        CRT_LAUNCH_P(true, true);
-    else if (gi)
-        CRT_LAUNCH_P(false, true);
+    if (gi) // built in crt_gi.cu (vector divisions through binary64)
+        crt_launch_persistent_gi(stats, SEEDED, SHADOWS, blocks, ctx->stream, &ctx->scene, sizeof ctx->scene, &dp, sizeof dp, ctx->d_pctl, patches_x, n_slots,
+                                 ctx->d_rgb, ctx->d_rgb8, ctx->d_counters, &ctx->wf.b, sizeof ctx->wf.b);
     else if (stats)
         CRT_LAUNCH_P(true, false);
     else

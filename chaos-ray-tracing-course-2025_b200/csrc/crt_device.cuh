@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/crt_cuda.h"
+#include "crt_sincos.h"
 
 namespace crtdev {
 
@@ -21,7 +22,8 @@ namespace crtdev {
 // right after it), which makes one index do for both; a leaf is {first reference, axis = 3 | count << 2}.  Half the
 // bytes of the 16-byte crt_kd_node: four nodes per 32-byte sector, siblings in the same sector, and a C4 walk tree of
 // 24 MB instead of 49 MB in L2.  kd_node_at() hands the kernels the {split, a, b, axis} / {0, first, count, 3} int4
-// they were written against.
+// they were written against.  OFF by default: measured on B200 the better hit rates do not pay for
+// the 16 extra instructions per node step on kernels that are bound by instruction issue (C4 2.97 -> 3.09 ms).
 #ifndef CRT_NODE8
 #define CRT_NODE8 0
 #endif
@@ -92,7 +94,31 @@ __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return V3{ a.x + b.x, a.y 
 __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return V3{ a.x - b.x, a.y - b.y, a.z - b.z }; }
 __device__ __forceinline__ V3 operator-(V3 a) { return V3{ -a.x, -a.y, -a.z }; }
 __device__ __forceinline__ V3 operator*(V3 a, float s) { return V3{ a.x * s, a.y * s, a.z * s }; }
-__device__ __forceinline__ V3 operator/(V3 a, float s) { return V3{ a.x / s, a.y / s, a.z / s }; }
+// a / s, three IEEE binary32 divisions by one denominator (normalisations, colour / area), two ways with the same bits:
+//   * binary32: three divisions.  Their fast path refuses a ZERO NUMERATOR (FCHK) and calls a ~50-instruction fix-up;
+//     with axis-aligned walls most normalisations have one (ncu r1zz, GI kernel: 13.7 M calls of the fix-up, 4.2 % of
+//     the issued instructions at 3 threads per instruction);
+//   * CRT_DIV_VIA_DOUBLE: each quotient as RN32 (RN64 (a * RN64 (1 / s))).  A quotient of two binary32 numbers lies at
+//     least 2^-48 (relative) away from every rounding boundary of binary32 unless it is exact, the binary64 product is
+//     within 2^-52 of it, so the final rounding lands on the correctly rounded quotient -- zeros, infinities, NaNs and
+//     subnormals included (tools/div_check.cpp: 3e8 operand pairs of every class; the GI parity tests compare the
+//     two against each other bit for bit).  No fix-up calls, but binary64 work: 15-01/scene2 with GI 211 -> 186 ms,
+//     the 1 M-triangle height field (no zero components anywhere) 2.95 -> 3.13 ms.
+// So it is a per-kernel choice made at compile time: the GI instantiations of k_render_persistent are built in their own
+// translation unit with CRT_DIV_VIA_DOUBLE = 1 (csrc/crt_gi.cu), everything else divides in binary32.  (Both paths in
+// one kernel behind a runtime flag were measured too: +16 % code, and the GI kernel, whose top stall is instruction
+// fetch, lost more than the division gained: 212 ms.)
+#ifndef CRT_DIV_VIA_DOUBLE
+#define CRT_DIV_VIA_DOUBLE 0
+#endif
+__device__ __forceinline__ V3 operator/(V3 a, float s) {
+#if CRT_DIV_VIA_DOUBLE
+    const double r = __drcp_rn(double(s));
+    return V3{ float(double(a.x) * r), float(double(a.y) * r), float(double(a.z) * r) };
+#else
+    return V3{ a.x / s, a.y / s, a.z / s };
+#endif
+}
 __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ V3 cross(V3 a, V3 b) { return V3{ a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x }; }
 __device__ __forceinline__ float length(V3 a) { return sqrtf(dot(a, a)); }
@@ -675,41 +701,16 @@ __device__ __forceinline__ Pcg32 make_pcg(uint32_t px, uint32_t py) {
     return rng;
 }
 
-// cosf/sinf of the reference go through glibc; binary64 sin/cos rounded once to binary32 agrees with it except
-// for rare last-bit cases (documented FP difference; only GI directions are affected, crt_renderer.cpp:68-74).
-// CRT_SINCOS_LEAN (default): the binary64 evaluation written out for the only arguments the renderer has, [0, 2 pi]
-// (pi * u and 2 pi * u with u in [0, 1)): quadrant by rint (a * 2/pi), two-step reduction with FMAs, the fdlibm kernel
-// polynomials on [-pi/4, pi/4] (error < 1 ulp of binary64, so the binary32 rounding agrees with the library call
-// except ~1e-8 of the time).  The library sincos() carries its large-argument path along: 7 % of the GI kernel's
-// issued instructions and a good part of its instruction-fetch stalls (profiles/r1z_ncu_source_c3gi_540x540_persistent.txt).
+// cosf/sinf of the reference go through glibc, which is not correctly rounded: over the 2 x 2^23 arguments the
+// renderer can produce it differs from binary64 sin/cos rounded once to binary32 on 1.3 % of them, in the last bit
+// (documented FP difference; only GI directions are affected, crt_renderer.cpp:68-74).
+// CRT_SINCOS_LEAN (default): crt_sincos.h, the same values as the library call below, without its large-argument path
 #ifndef CRT_SINCOS_LEAN
 #define CRT_SINCOS_LEAN 1
 #endif
 __device__ __forceinline__ void sincos_ref(float a, float &s, float &c) {
 #if CRT_SINCOS_LEAN
-    const double x = double(a);
-    const double k = rint(x * 6.36619772367581382433e-01);
-    double r = __fma_rn(-k, 1.57079632679489655800e+00, x);
-    r = __fma_rn(-k, 6.12323399573676603587e-17, r);
-    const double z = r * r;
-    double ps = 1.58969099521155010221e-10;
-    ps = __fma_rn(ps, z, -2.50507602534068634195e-08);
-    ps = __fma_rn(ps, z, 2.75573137070700676789e-06);
-    ps = __fma_rn(ps, z, -1.98412698298579493134e-04);
-    ps = __fma_rn(ps, z, 8.33333333332248946124e-03);
-    ps = __fma_rn(ps, z, -1.66666666666666324348e-01);
-    const double sr = __fma_rn(ps * z, r, r);
-    double pc = -1.13596475577881948265e-11;
-    pc = __fma_rn(pc, z, 2.08757232129817482790e-09);
-    pc = __fma_rn(pc, z, -2.75573143513906633035e-07);
-    pc = __fma_rn(pc, z, 2.48015872894767294178e-05);
-    pc = __fma_rn(pc, z, -1.38888888888741095749e-03);
-    pc = __fma_rn(pc, z, 4.16666666666666019037e-02);
-    const double cr = __fma_rn(pc * z, z, __fma_rn(-0.5, z, 1.0));
-    const int q = int(k) & 3;
-    const double sq = (q & 1) ? cr : sr, cq = (q & 1) ? sr : cr;
-    s = float((q & 2) ? -sq : sq);
-    c = float(((q + 1) & 2) ? -cq : cq);
+    sincos_0_2pi(a, s, c);
 #else
     double sd, cd;
     sincos(double(a), &sd, &cd);
