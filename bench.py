@@ -37,6 +37,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import numpy as np  # noqa: E402
 
+_JSON_OUT = None  # N > 1: a duplicate of the original stdout (see run_ours)
+
 WORKLOADS = {
     # name: (description, width, height, max_ray_depth, sample size for the CPU arm)
     "c4": ("synthetic 1002528-triangle height field, reflective, 3840x2160, max_ray_depth 8, 1 point light", 3840, 2160, 8, (1920, 1080)),
@@ -204,6 +206,12 @@ def run_ours(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version / warning lines stay off stdout: ONE JSON line there
+        # ... and since NCCL still writes its version line to file descriptor 1 on some boxes (r1zz, N = 2), the
+        # descriptor itself points at stderr from here on; the JSON line goes to a duplicate of the original stdout
+        global _JSON_OUT
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=device)
 
     desc, W, H, depth, _ = WORKLOADS[args.workload]
@@ -418,7 +426,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 72 + 56, "d2h_bytes_per_step": rows_local * W * 12,
                     "ms_per_step": t_e2e / e2e_steps * 1e3},
             "gpu_launches": (kernel_launches + (1 if peer is not None else 0)) * args.steps}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
