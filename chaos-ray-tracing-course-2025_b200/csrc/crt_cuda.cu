@@ -10,7 +10,11 @@
 
 #include "crt_kernels.cuh"
 #include "crt_wavefront.cuh"
+#ifndef CRT_PERSIST_CLASSIC
 #include "crt_persistent.cuh"
+#else
+#include "crt_persistent_classic.cuh" // round 1's walker inside the persistent kernel (A/B builds only)
+#endif
 #include "crt_ppm.cuh"
 #include "crt_push.cuh"
 #include "crt_gi.h"
@@ -484,7 +488,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         { s->vert_normal, size_t(s->n_vertices) * sizeof(crt_float4), 0 },
         { s->vert_uv, size_t(s->n_vertices) * 2 * sizeof(float), 0 },
         { s->box_nodes, size_t(s->n_nodes) * sizeof(crt_box_node), 0 },
-        { s->fast_nodes, size_t(s->n_fast_nodes) * sizeof(KdNodeRec), 0 }, // CRT_NODE8: packed below, not copied
+        { s->fast_nodes, size_t(s->n_fast_nodes) * sizeof(KdNodeRec), 0 }, // + the empty leaf; CRT_NODE8: packed below, not copied
         { s->refs, size_t(s->n_refs) * sizeof(uint32_t), 0 },
         { s->lights, size_t(s->n_lights) * sizeof(crt_float4), 0 },
         { s->materials, size_t(s->n_materials) * sizeof(crt_material), 0 },
@@ -497,7 +501,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         if (p.bytes && !p.src)
             return fail(ctx, CRT_ERR_INVALID, "scene array pointer is NULL");
         p.offset = total;
-        total += align_up(p.bytes ? p.bytes : 16, 256);
+        total += align_up((p.bytes ? p.bytes : 16) + (&p == &parts[5] ? sizeof(KdNodeRec) : 0), 256);
     }
     if (total > ctx->d_arena_cap) {
         cudaFree(ctx->d_arena);
@@ -519,6 +523,11 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
 #if CRT_NODE8
     if (const char *why = pack_walk_nodes(s->fast_nodes, s->n_fast_nodes, reinterpret_cast<int2 *>(ctx->h_arena + parts[5].offset)))
         return fail(ctx, CRT_ERR_INVALID, why);
+    reinterpret_cast<int2 *>(ctx->h_arena + parts[5].offset)[s->n_fast_nodes] = make_int2(0, 3);
+#else
+    // one node more than the builder made: a leaf without triangles.  A lane whose pending subtree a helper lane took
+    // over finds this node in its stack instead (crt_trace_lean.cuh: lean_steal), so a visit never tests for theft
+    reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset)[s->n_fast_nodes] = make_int4(0, 0, 0, 3);
 #endif
     CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena, ctx->h_arena, total, cudaMemcpyHostToDevice, ctx->stream));
 
@@ -530,6 +539,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     std::memcpy(d.root_min, s->root_min, sizeof d.root_min);
     std::memcpy(d.root_max, s->root_max, sizeof d.root_max);
     d.n_triangles = s->n_triangles, d.n_nodes = s->n_nodes, d.n_lights = s->n_lights, d.n_materials = s->n_materials, d.n_textures = s->n_textures;
+    d.kd_empty_leaf = s->n_fast_nodes;
     d.tri_verts = reinterpret_cast<const float4 *>(ctx->d_arena + parts[0].offset);
     d.tri_meta = reinterpret_cast<const int4 *>(ctx->d_arena + parts[1].offset);
     d.vert_normal = reinterpret_cast<const float4 *>(ctx->d_arena + parts[2].offset);
@@ -559,6 +569,8 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // r1z_packet_sweep.txt: height fields covering a quarter of the frame): 5-25 % ahead of the per-lane walk from ~60
     // frame pixels per triangle upwards (C1 0.19 -> 0.17 ms, C3 0.82 -> 0.63 ms, C5 0.69 -> 0.63 ms), 1.3-3x BEHIND it
     // below 20 (C4: 8 pixels per triangle).  Threshold 64; $CRT_PACKET=0|1 overrides.
+    if (const char *k = std::getenv("CRT_WALKER"); k && *k)
+        ctx->wf.classic_walker = std::strcmp(k, "classic") == 0;
     ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)
     if (const char *k = std::getenv("CRT_PACKET"); k && *k)
         ctx->packet_mode = *k == '1' ? 1 : 0;

@@ -41,6 +41,7 @@ struct DScene {
     int gi_on, reflections_on, refractions_on;
     float root_min[3], root_max[3];
     int n_triangles, n_nodes, n_lights, n_materials, n_textures;
+    int kd_empty_leaf; // index of a leaf without triangles that the upload appends to the walk tree (tombstone of stolen subtrees)
     const float4 *__restrict__ tri_verts;   // 3 per triangle
     const int4 *__restrict__ tri_meta;      // 1 per triangle
     const float4 *__restrict__ vert_normal; // 1 per vertex

@@ -95,9 +95,10 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     const float gi_div = float(P.gi_rays + 1u);
     auto no_shadow = [](V3, float) { return false; };
 
-    TraceWalker w;
+    crtwalk::LeanWalker w;
     uint2 spill[kStack]; // stack entries below the shared-memory window
-    w.node = -1, w.sp = 0, w.lo = 0, w.flagged = 0;
+    w.node = crtwalk::kDone, w.sp = 1, w.lo = 0, w.flagged = 0, w.tmin = 0.0f, w.tmax = 0.0f;
+    const uint32_t empty_leaf = uint32_t(S.kd_empty_leaf);
     // ---- pixel state
     int px = 0, ply = -1; // my pixel (local row), ply < 0 = no pixel
     int depth = 0;
@@ -111,13 +112,13 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     bool exhausted = false;
     unsigned src = lane;
     bool helper = false;
-    int stolen = 0;
+    int stolen = 1;   // entries [1, stolen) of my stack are tombstones (helpers took them over)
     int patience = 0; // rounds some lane has been waiting for a SHADE phase (warp-uniform)
 
     for (;;) {
         // ---- refill: idle lanes take the next pixel slots
         const unsigned busy = __ballot_sync(full, ply >= 0 || helper);
-        if (!exhausted && __popc(busy) < CRT_L_REFILL) {
+        if (!exhausted && __popc(busy) < CRT_N_REFILL) {
             const unsigned idle = ~busy;
             int base = 0;
             if (lane == 0)
@@ -133,9 +134,9 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                         x = slot, ly = 0; // px = index of my seed ray within its level
                     px = x, ply = ly, depth = base_depth;
                     fresh = true, live = false;
-                    src = lane, stolen = 0;
+                    src = lane, stolen = 1;
                     ws.helpers[lane] = 0;
-                    w.node = -1;
+                    w.node = crtwalk::kDone;
                     p0_count = 0, p1_count = 0;
                 }
             }
@@ -147,139 +148,33 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
             continue;
         }
         // ---- the queue is empty and some lanes have nothing to do: they take over pending subtrees of the lanes that
-        //      are still walking (the BOTTOM stack entry = the farthest, usually largest piece of the remaining path).
-        //      A bounce level ends with its longest ray; a skimming ray crosses ~1000 cells one dependent load at a
-        //      time, and this spreads that walk over the warp.  The victim's entry becomes a tombstone (its entry
-        //      distance still bounds the entry above it); hits merge through the owner's ws.best as always.
-        if (exhausted) {
-            const unsigned thieves = __ballot_sync(full, ply < 0 && !helper);
-            stolen = min(stolen, w.sp); // entries below `stolen` are tombstones; popping past them frees the slots
-            const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
-            const bool can_give = (ply >= 0 || helper) && w.node != -1 && w.lo == 0 && w.sp - stolen >= 2 && lowest < uint32_t(kStolenNode);
-            const unsigned victims = __ballot_sync(full, can_give);
-            if (thieves != 0u && victims != 0u) {
-                const int pairs = min(__popc(thieves), __popc(victims));
-                const bool thief = ply < 0 && !helper;
-                const int rank = thief ? __popc(thieves & lt_mask) : (can_give ? __popc(victims & lt_mask) : 32);
-                const bool paired = rank < pairs;
-                const unsigned v = (paired && thief) ? __fns(victims, 0, rank + 1) : lane; // the rank-th victim
-                const unsigned v_src = __shfl_sync(full, src, v);
-                const float v_root_exit = __shfl_sync(full, w.root_tmax, v);
-                const int v_stolen = __shfl_sync(full, stolen, v);
-                if (paired && thief) {
-                    const uint2 e = ws.stack[v_stolen & (kWin - 1)][v];
-                    // exit distance of that entry = entry distance of the one below it (tombstones keep theirs)
-                    const float exit_t = v_stolen == 0 ? v_root_exit : __uint_as_float(ws.stack[(v_stolen - 1) & (kWin - 1)][v].y);
-                    helper = true;
-                    src = v_src;
-                    stolen = 0;
-                    w.sp = 0, w.lo = 0, w.flagged = 0;
-                    w.node = int(e.x);
-                    w.tmin = __uint_as_float(e.y);
-                    w.tmax = exit_t, w.root_tmax = exit_t;
-                    atomicAdd(&ws.helpers[v_src], 1);
-                    if (STATS)
-                        ++cn.node_tests;
-                }
-                __syncwarp();
-                if (paired && !thief) {
-                    ws.stack[stolen & (kWin - 1)][lane].x = uint32_t(kStolenNode);
-                    ++stolen;
-                }
-                __syncwarp();
-            }
-        }
-        // ---- walk: a few node visits per lane; a leaf is parked and the walk goes on (speculatively: the
-        //      leaf's triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong)
+        //      are still walking (crt_trace_lean.cuh: lean_steal)
+        if (exhausted)
+            lean_steal<STATS>(ws, w, lane, lt_mask, ply >= 0, helper, src, stolen, empty_leaf, cn);
+        // ---- walk: a few node visits per lane; a leaf is parked and the walk goes on (crt_trace_lean.cuh: lean_walk)
         bool blocked = false;
-        if ((ply >= 0 || helper) && w.node != -1) { // fresh pixels have w.node == -1
-            const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
-#pragma unroll
-            for (int k = 0; k < (GI ? CRT_P_STEPS_GI : CRT_P_STEPS); ++k) {
-                if (w.node == -1 || blocked)
-                    break;
-                bool need_pop = w.prune_at_visit(best_t);
-                if (!need_pop) {
-                    const int4 n = kd_node_at(S, w.node);
-                    if (n.w == 3) {
-                        if (p1_count == 0) {
-                            if (p0_count == 0)
-                                p0_first = n.y, p0_count = n.z;
-                            else
-                                p1_first = n.y, p1_count = n.z;
-                            need_pop = true;
-                        } else {
-                            blocked = true; // both slots taken: wait for the test phase below
-                        }
-                    } else {
-                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn);
-                        need_pop = w.node < 0;
-                    }
-                }
-                if (need_pop)
-                    w.pop_fast<STATS>(ws, spill, lane, cn);
-            }
-        }
+        if ((ply >= 0 || helper) && !w.done()) // fresh pixels have a finished walk
+            blocked = lean_walk<STATS, (GI ? CRT_P_STEPS_GI : CRT_P_STEPS)>(S, ws, w, spill, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
         // ---- test phase: all parked leaves of all lanes at once
         const unsigned parked = __ballot_sync(full, p0_count > 0);
-        const unsigned walkers = __ballot_sync(full, (ply >= 0 || helper) && w.node != -1 && !blocked);
-        const unsigned waiting = __ballot_sync(full, (ply >= 0 || helper) && w.node == -1 && p0_count > 0);
-        const bool fire = parked != 0u && (__popc(parked) >= CRT_L_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_L_WAITERS);
+        const unsigned walkers = __ballot_sync(full, (ply >= 0 || helper) && !w.done() && !blocked);
+        const unsigned waiting = __ballot_sync(full, (ply >= 0 || helper) && w.done() && p0_count > 0);
+        const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_N_WAITERS);
         if (fire) {
-            const int mine = p0_count + p1_count;
-            int incl = mine;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(full, incl, o);
-                if (int(lane) >= o)
-                    incl += v;
-            }
-            const int items = __shfl_sync(full, incl, 31);
-            const int excl = incl - mine;
-            for (int base_item = 0; base_item < items; base_item += 32) {
-                const int item = base_item + int(lane);
-                // owner = last lane whose exclusive prefix is <= item; lanes with equal prefixes have nothing parked
-                // except the last of the run, which owns the item
-                int owner = 0;
-#pragma unroll
-                for (int stride = 16; stride > 0; stride >>= 1) {
-                    const int probe = __shfl_sync(full, excl, owner + stride);
-                    if (probe <= item)
-                        owner += stride;
-                }
-                const int o_excl = __shfl_sync(full, excl, owner);
-                const int o_first0 = __shfl_sync(full, p0_first, owner), o_count0 = __shfl_sync(full, p0_count, owner);
-                const int o_first1 = __shfl_sync(full, p1_first, owner);
-                owner = int(__shfl_sync(full, src, owner)); // a helper's leaves are tested against the ray it helps
-                if (item < items) {
-                    const int k = item - o_excl;
-                    const uint32_t ref = __ldg(&S.kd_refs[k < o_count0 ? o_first0 + k : o_first1 + (k - o_count0)]);
-                    const int tri = int(ref & 0x7FFFFFFFu);
-                    const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
-                    const V3 o = mk(ws.ray[0][owner], ws.ray[1][owner], ws.ray[2][owner]), d = mk(ws.ray[3][owner], ws.ray[4][owner], ws.ray[5][owner]);
-                    if (STATS)
-                        ++cn.tri_tests;
-                    float t;
-                    if (triangle_test_flat(A, B, C, (ref >> 31) != 0, o, d, t)) {
-                        t = t + 0.0f; // -0 -> +0 so the bit pattern orders like the value
-                        atomicMin(&ws.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)uint32_t(tri));
-                    }
-                }
-            }
-            __syncwarp();
+            lean_test_parked<STATS>(S, ws, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
             p0_count = 0, p1_count = 0;
         }
         // ---- helpers that finished hand their subtree's result back (it is already merged into the owner's best)
-        if (helper && w.node == -1 && p0_count == 0) {
+        if (helper && w.done() && p0_count == 0) {
             atomicSub(&ws.helpers[src], 1);
             helper = false;
             src = lane;
         }
         __syncwarp();
         // ---- SHADE phase: lanes whose query is finished (or whose pixel is new) continue their pixel's recursion
-        const bool ready = ply >= 0 && w.node == -1 && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
+        const bool ready = ply >= 0 && w.done() && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
         const unsigned ready_m = __ballot_sync(full, ready);
-        const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && w.node != -1);
+        const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && !w.done());
         patience = ready_m != 0u ? patience + 1 : 0;
         if (ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u || patience >= (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE))) {
             patience = 0;
@@ -314,10 +209,10 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                         }
                         const RaySetup q = ray_setup(S, ray);
                         if (q.live) { // leave the phase: the walk answers this query
-                            w.start(ws, lane, ray.o, ray.d, q.inv, q.tmin, q.tmax);
+                            w.start(ws, lane, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, q.inv.x, q.inv.y, q.inv.z, q.tmin, q.tmax);
                             ws.best[lane] = kNoHitKey;
                             live = true;
-                            stolen = 0;
+                            stolen = 1;
                             break;
                         }
                         live = false; // misses the root box (or NaN direction): a finished query without a hit
@@ -332,10 +227,10 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                         shadow_q = true;
                         const RaySetup q = ray_setup(S, ray);
                         if (q.live) {
-                            w.start(ws, lane, ray.o, ray.d, q.inv, q.tmin, q.tmax);
+                            w.start(ws, lane, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, q.inv.x, q.inv.y, q.inv.z, q.tmin, q.tmax);
                             ws.best[lane] = kNoHitKey;
                             live = true;
-                            stolen = 0;
+                            stolen = 1;
                             break;
                         }
                         live = false;

@@ -1,0 +1,490 @@
+// PERSISTENT per-pixel pipeline: one kernel renders the frame.  A lane owns a PIXEL and keeps it through the whole
+// recursion of shade_ray (src/core/crt_renderer.cpp:46-145), depth-first with the explicit frame stack of
+// k_render_mega (crt_kernels.cuh) -- so evaluation order, RNG order (one PCG32 stream per pixel, crt_random.h) and
+// the nesting in which colours are combined are the reference's -- while the closest-hit queries are served by the
+// warp-cooperative walk of k_wf_trace_light: speculative walk, leaves parked and tested warp-wide, work stealing.
+//
+// Why (ncu r1p): the level-synchronous wavefront pays one tail per bounce level (levels 2-8 of C4 hold
+// 18 % of the rays and take 55 % of the frame) and cannot run GI at all; the per-pixel megakernel can, but its lanes
+// sit in unrelated phases of trace / shade code (300 Mrays/s on the GI scene).  Here a warp alternates between three
+// phases, each entered only when enough lanes want it:
+//   WALK   every lane with an unfinished query visits up to CRT_P_STEPS nodes (CRT_P_STEPS_GI with GI);
+//   TEST   parked leaves of all lanes, one (ray, triangle) pair per lane and iteration;
+//   SHADE  lanes whose query is finished run the continuation of their pixel's recursion: shade the hit, then either
+//          start the next query (reflection, refraction, GI child, sibling) or finish the pixel and take a new one.
+#pragma once
+
+namespace crtdev {
+
+#ifndef CRT_P_MINBLOCKS
+#define CRT_P_MINBLOCKS 7
+#endif
+#ifndef CRT_P_MINBLOCKS_GI
+#define CRT_P_MINBLOCKS_GI 8 // 64 registers: the GI continuation (sinf / cosf, PCG state) spills a few values, the walk does not
+#endif
+#ifndef CRT_P_PATIENCE_GI
+#define CRT_P_PATIENCE_GI 16
+#endif
+#ifndef CRT_P_PATIENCE
+#define CRT_P_PATIENCE 8
+#endif
+#ifndef CRT_P_STEPS
+#define CRT_P_STEPS 6
+#endif
+#ifndef CRT_P_STEPS_GI
+#define CRT_P_STEPS_GI 2 // GI queries are short (a diffuse bounce ends at the next surface): more frequent phase changes pay
+#endif
+#ifndef CRT_P_SHADE_TRIGGER_GI
+#define CRT_P_SHADE_TRIGGER_GI 28 // the GI continuation is long (sinf / cosf, basis, PCG): run it for nearly full warps only
+#endif
+#ifndef CRT_P_SHADE_TRIGGER
+#define CRT_P_SHADE_TRIGGER 12
+#endif
+
+struct PersistCtl {
+    int next_slot; // pixel slots handed out so far
+};
+
+// slot -> pixel, 8x4 patches, patches row-major (neighbouring slots are neighbouring pixels)
+__device__ __forceinline__ bool persist_slot_pixel(int slot, int patches_x, int width, int rows, int &x, int &ly) {
+    const int patch = slot >> 5, l = slot & 31;
+    x = (patch % patches_x) * 8 + (l & 7);
+    ly = (patch / patches_x) * 4 + (l >> 3);
+    return x < width && ly < rows;
+}
+
+// one light of add_direct_light (crt_device.cuh), same operation sequence
+struct LightTerm {
+    V3 dir;
+    float r2, cos_law, area, intensity;
+};
+__device__ __forceinline__ LightTerm light_term(const DScene &S, int i, V3 Pnt, V3 n) {
+    const float four_pi = 4.0f * 3.14159274101257324219f;
+    const float4 L = __ldg(&S.lights[i]);
+    LightTerm t;
+    V3 dir = xyz(L) - Pnt;
+    t.r2 = dot(dir, dir);
+    t.dir = dir / sqrtf(t.r2);
+    const float ln = dot(t.dir, n);
+    t.cos_law = (0.0f < ln) ? ln : 0.0f;
+    t.area = four_pi * t.r2;
+    t.intensity = L.w;
+    return t;
+}
+
+// SEEDED: the work items are not pixels but the level-1 rays the wavefront's level-0 shade stage queued (hybrid
+// pipeline: the dense, coherent primary level runs as raygen / trace / shade kernels at full SIMD width, everything
+// deeper runs here).  A lane takes a level-1 ray, evaluates its whole subtree depth-first and stores the subtree's
+// colour in the level-1 node record, which the level-0 resolve kernel combines as before.
+template <bool STATS, bool GI, bool SEEDED, bool SHADOWS>
+__global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_MINBLOCKS) k_render_persistent(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
+                                                                                    PersistCtl *__restrict__ ctl, int patches_x, int n_slots_arg,
+                                                                                    float *__restrict__ rgb, uint8_t *__restrict__ rgb8,
+                                                                                    Counters *__restrict__ counters, const __grid_constant__ WfBuffers b) {
+    // SEEDED: `patches_x` carries the bounce level whose queued rays are the seeds (1 = everything below the primary level)
+    const int base_depth = SEEDED ? patches_x : 0;
+    const int seed_start = SEEDED ? level_start(b.ctl, base_depth) : 0;
+    const int n_slots = SEEDED ? level_count(b.ctl, b.cap, base_depth, seed_start) : n_slots_arg;
+    Counters cn{};
+    __shared__ LightWarpShared shared[kTraceWarps];
+    LightWarpShared &ws = shared[threadIdx.x >> 5];
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned full = 0xffffffffu;
+    const V3 bg = mk(S.bg[0], S.bg[1], S.bg[2]);
+    const float gi_div = float(P.gi_rays + 1u);
+    auto no_shadow = [](V3, float) { return false; };
+
+    TraceWalker w;
+    uint2 spill[kStack]; // stack entries below the shared-memory window
+    w.node = -1, w.sp = 0, w.lo = 0, w.flagged = 0;
+    // ---- pixel state
+    int px = 0, ply = -1; // my pixel (local row), ply < 0 = no pixel
+    int depth = 0;
+    bool live = false;    // the current query entered the root box (its result is in ws.best[lane])
+    bool fresh = false;   // pixel just taken: its primary ray has not been generated yet (done in the SHADE phase)
+    bool shadow_q = false; // the running query is a shadow ray of frames[depth]'s light loop, not a shade_ray call
+    Pcg32 rng{};
+    Frame frames[kMaxDepthCap + 1];
+    // ---- walk state (see k_wf_trace_light)
+    int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0;
+    bool exhausted = false;
+    unsigned src = lane;
+    bool helper = false;
+    int stolen = 0;
+    int patience = 0; // rounds some lane has been waiting for a SHADE phase (warp-uniform)
+
+    for (;;) {
+        // ---- refill: idle lanes take the next pixel slots
+        const unsigned busy = __ballot_sync(full, ply >= 0 || helper);
+        if (!exhausted && __popc(busy) < CRT_L_REFILL) {
+            const unsigned idle = ~busy;
+            int base = 0;
+            if (lane == 0)
+                base = atomicAdd(&ctl->next_slot, __popc(idle));
+            base = __shfl_sync(full, base, 0);
+            if (base + __popc(idle) >= n_slots)
+                exhausted = true;
+            if (ply < 0 && !helper) {
+                const int slot = base + __popc(idle & lt_mask);
+                int x, ly;
+                if (slot < n_slots && (SEEDED || persist_slot_pixel(slot, patches_x, S.cam.width, P.rows, x, ly))) {
+                    if (SEEDED)
+                        x = slot, ly = 0; // px = index of my seed ray within its level
+                    px = x, ply = ly, depth = base_depth;
+                    fresh = true, live = false;
+                    src = lane, stolen = 0;
+                    ws.helpers[lane] = 0;
+                    w.node = -1;
+                    p0_count = 0, p1_count = 0;
+                }
+            }
+            __syncwarp();
+        }
+        if (__ballot_sync(full, ply >= 0 || helper) == 0u) {
+            if (exhausted)
+                break;
+            continue;
+        }
+        // ---- the queue is empty and some lanes have nothing to do: they take over pending subtrees of the lanes that
+        //      are still walking (the BOTTOM stack entry = the farthest, usually largest piece of the remaining path).
+        //      A bounce level ends with its longest ray; a skimming ray crosses ~1000 cells one dependent load at a
+        //      time, and this spreads that walk over the warp.  The victim's entry becomes a tombstone (its entry
+        //      distance still bounds the entry above it); hits merge through the owner's ws.best as always.
+        if (exhausted) {
+            const unsigned thieves = __ballot_sync(full, ply < 0 && !helper);
+            stolen = min(stolen, w.sp); // entries below `stolen` are tombstones; popping past them frees the slots
+            const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
+            const bool can_give = (ply >= 0 || helper) && w.node != -1 && w.lo == 0 && w.sp - stolen >= 2 && lowest < uint32_t(kStolenNode);
+            const unsigned victims = __ballot_sync(full, can_give);
+            if (thieves != 0u && victims != 0u) {
+                const int pairs = min(__popc(thieves), __popc(victims));
+                const bool thief = ply < 0 && !helper;
+                const int rank = thief ? __popc(thieves & lt_mask) : (can_give ? __popc(victims & lt_mask) : 32);
+                const bool paired = rank < pairs;
+                const unsigned v = (paired && thief) ? __fns(victims, 0, rank + 1) : lane; // the rank-th victim
+                const unsigned v_src = __shfl_sync(full, src, v);
+                const float v_root_exit = __shfl_sync(full, w.root_tmax, v);
+                const int v_stolen = __shfl_sync(full, stolen, v);
+                if (paired && thief) {
+                    const uint2 e = ws.stack[v_stolen & (kWin - 1)][v];
+                    // exit distance of that entry = entry distance of the one below it (tombstones keep theirs)
+                    const float exit_t = v_stolen == 0 ? v_root_exit : __uint_as_float(ws.stack[(v_stolen - 1) & (kWin - 1)][v].y);
+                    helper = true;
+                    src = v_src;
+                    stolen = 0;
+                    w.sp = 0, w.lo = 0, w.flagged = 0;
+                    w.node = int(e.x);
+                    w.tmin = __uint_as_float(e.y);
+                    w.tmax = exit_t, w.root_tmax = exit_t;
+                    atomicAdd(&ws.helpers[v_src], 1);
+                    if (STATS)
+                        ++cn.node_tests;
+                }
+                __syncwarp();
+                if (paired && !thief) {
+                    ws.stack[stolen & (kWin - 1)][lane].x = uint32_t(kStolenNode);
+                    ++stolen;
+                }
+                __syncwarp();
+            }
+        }
+        // ---- walk: a few node visits per lane; a leaf is parked and the walk goes on (speculatively: the
+        //      leaf's triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong)
+        bool blocked = false;
+        if ((ply >= 0 || helper) && w.node != -1) { // fresh pixels have w.node == -1
+            const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
+#pragma unroll
+            for (int k = 0; k < (GI ? CRT_P_STEPS_GI : CRT_P_STEPS); ++k) {
+                if (w.node == -1 || blocked)
+                    break;
+                bool need_pop = w.prune_at_visit(best_t);
+                if (!need_pop) {
+                    const int4 n = kd_node_at(S, w.node);
+                    if (n.w == 3) {
+                        if (p1_count == 0) {
+                            if (p0_count == 0)
+                                p0_first = n.y, p0_count = n.z;
+                            else
+                                p1_first = n.y, p1_count = n.z;
+                            need_pop = true;
+                        } else {
+                            blocked = true; // both slots taken: wait for the test phase below
+                        }
+                    } else {
+                        w.step<STATS>(ws, spill, lane, src, n, best_t, cn);
+                        need_pop = w.node < 0;
+                    }
+                }
+                if (need_pop)
+                    w.pop_fast<STATS>(ws, spill, lane, cn);
+            }
+        }
+        // ---- test phase: all parked leaves of all lanes at once
+        const unsigned parked = __ballot_sync(full, p0_count > 0);
+        const unsigned walkers = __ballot_sync(full, (ply >= 0 || helper) && w.node != -1 && !blocked);
+        const unsigned waiting = __ballot_sync(full, (ply >= 0 || helper) && w.node == -1 && p0_count > 0);
+        const bool fire = parked != 0u && (__popc(parked) >= CRT_L_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_L_WAITERS);
+        if (fire) {
+            const int mine = p0_count + p1_count;
+            int incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(full, incl, o);
+                if (int(lane) >= o)
+                    incl += v;
+            }
+            const int items = __shfl_sync(full, incl, 31);
+            const int excl = incl - mine;
+            for (int base_item = 0; base_item < items; base_item += 32) {
+                const int item = base_item + int(lane);
+                // owner = last lane whose exclusive prefix is <= item; lanes with equal prefixes have nothing parked
+                // except the last of the run, which owns the item
+                int owner = 0;
+#pragma unroll
+                for (int stride = 16; stride > 0; stride >>= 1) {
+                    const int probe = __shfl_sync(full, excl, owner + stride);
+                    if (probe <= item)
+                        owner += stride;
+                }
+                const int o_excl = __shfl_sync(full, excl, owner);
+                const int o_first0 = __shfl_sync(full, p0_first, owner), o_count0 = __shfl_sync(full, p0_count, owner);
+                const int o_first1 = __shfl_sync(full, p1_first, owner);
+                owner = int(__shfl_sync(full, src, owner)); // a helper's leaves are tested against the ray it helps
+                if (item < items) {
+                    const int k = item - o_excl;
+                    const uint32_t ref = __ldg(&S.kd_refs[k < o_count0 ? o_first0 + k : o_first1 + (k - o_count0)]);
+                    const int tri = int(ref & 0x7FFFFFFFu);
+                    const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
+                    const V3 o = mk(ws.ray[0][owner], ws.ray[1][owner], ws.ray[2][owner]), d = mk(ws.ray[3][owner], ws.ray[4][owner], ws.ray[5][owner]);
+                    if (STATS)
+                        ++cn.tri_tests;
+                    float t;
+                    if (triangle_test_flat(A, B, C, (ref >> 31) != 0, o, d, t)) {
+                        t = t + 0.0f; // -0 -> +0 so the bit pattern orders like the value
+                        atomicMin(&ws.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)uint32_t(tri));
+                    }
+                }
+            }
+            __syncwarp();
+            p0_count = 0, p1_count = 0;
+        }
+        // ---- helpers that finished hand their subtree's result back (it is already merged into the owner's best)
+        if (helper && w.node == -1 && p0_count == 0) {
+            atomicSub(&ws.helpers[src], 1);
+            helper = false;
+            src = lane;
+        }
+        __syncwarp();
+        // ---- SHADE phase: lanes whose query is finished (or whose pixel is new) continue their pixel's recursion
+        const bool ready = ply >= 0 && w.node == -1 && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
+        const unsigned ready_m = __ballot_sync(full, ready);
+        const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && w.node != -1);
+        patience = ready_m != 0u ? patience + 1 : 0;
+        if (ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u || patience >= (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE))) {
+            patience = 0;
+            if (ready) {
+                int act = 0; // 0: consume the finished query, 1: shade_ray(ray, depth) entry, 2: return c to the callers
+                Ray ray{};
+                V3 c = mk(0.0f, 0.0f, 0.0f);
+                if (fresh) {
+                    fresh = false;
+                    if (SEEDED) {
+                        ray = Ray{ xyz(b.ray_o[seed_start + px]), xyz(b.ray_d[seed_start + px]) };
+                    } else {
+                        const int y = global_row(P, ply);
+                        if (GI)
+                            rng = make_pcg(uint32_t(px), uint32_t(y));
+                        ray = generate_ray(S.cam, px, y);
+                    }
+                    depth = base_depth;
+                    act = 1;
+                }
+                for (;;) {
+                    if (act == 1) {
+                        if (uint32_t(depth) > P.max_ray_depth) { // crt_renderer.cpp:47-48: black before tracing
+                            c = mk(0.0f, 0.0f, 0.0f);
+                            act = 2;
+                            continue;
+                        }
+                        if (STATS) {
+                            ++cn.rays;
+                            ++cn.rays_by_depth[depth];
+                            ++cn.node_tests;
+                        }
+                        const RaySetup q = ray_setup(S, ray);
+                        if (q.live) { // leave the phase: the walk answers this query
+                            w.start(ws, lane, ray.o, ray.d, q.inv, q.tmin, q.tmax);
+                            ws.best[lane] = kNoHitKey;
+                            live = true;
+                            stolen = 0;
+                            break;
+                        }
+                        live = false; // misses the root box (or NaN direction): a finished query without a hit
+                        act = 0;
+                        continue;
+                    }
+                    if (act == 3) { // shadow query of the light loop (flagged mode, crt_renderer.cpp:88-92 as intended)
+                        if (STATS) {
+                            ++cn.shadow_rays;
+                            ++cn.node_tests;
+                        }
+                        shadow_q = true;
+                        const RaySetup q = ray_setup(S, ray);
+                        if (q.live) {
+                            w.start(ws, lane, ray.o, ray.d, q.inv, q.tmin, q.tmax);
+                            ws.best[lane] = kNoHitKey;
+                            live = true;
+                            stolen = 0;
+                            break;
+                        }
+                        live = false;
+                        act = 0;
+                        continue;
+                    }
+                    if (act == 0) {
+                        Hit h{ kInf, -1 };
+                        if (live) {
+                            const unsigned long long key = ws.best[lane];
+                            h.t = __uint_as_float(unsigned(key >> 32));
+                            h.tri = int(unsigned(key & 0xffffffffull));
+                            ray = Ray{ mk(ws.ray[0][lane], ws.ray[1][lane], ws.ray[2][lane]), mk(ws.ray[3][lane], ws.ray[4][lane], ws.ray[5][lane]) };
+                        }
+                        live = false;
+                        if (SHADOWS && shadow_q) { // lit iff nothing is hit within the light's distance; then the next light
+                            shadow_q = false;
+                            Frame &f = frames[depth];
+                            const LightTerm lt = light_term(S, f.i, f.b, f.c);
+                            if (!(h.tri >= 0 && !(h.t * h.t > lt.r2)))
+                                f.a = f.a + ((f.g * lt.intensity) / lt.area) * lt.cos_law;
+                            ++f.i;
+                            if (f.i < S.n_lights) {
+                                ray = Ray{ f.b + f.c * P.shadow_bias, light_term(S, f.i, f.b, f.c).dir };
+                                act = 3;
+                            } else {
+                                c = f.a / gi_div;
+                                act = 2;
+                            }
+                            continue;
+                        }
+                        act = 2;
+                        if (h.tri < 0) {
+                            c = bg;
+                            continue;
+                        }
+                        const Surface s = make_surface(S, ray, h);
+                        const int4 m = __ldg(&S.materials[s.material]);
+                        Frame &f = frames[depth];
+                        if (m.x == 0) { // Diffuse
+                            const V3 albedo = sample_texture(S, m.y, s);
+                            if (GI) {
+                                f.kind = kDiffuseGi, f.i = 0;
+                                f.a = mk(0.0f, 0.0f, 0.0f), f.b = s.P, f.c = s.n, f.e = ray.d, f.g = albedo;
+                                if (uint32_t(depth) + 1u > P.max_ray_depth) {
+                                    // every bounce ray of this surface lies beyond max depth: shade_ray returns black
+                                    // before tracing (crt_renderer.cpp:47-48), so their directions are never used and
+                                    // only the pixel's generator moves on, two draws per ray (:66-70).  This is the
+                                    // last level, i.e. most of the rays of a GI frame (74 % in 15-01/scene2): skipping
+                                    // 4 x (two binary64 sincos, a cross product, two normalisations) per hit.
+                                    for (uint32_t k = 0; k < 2u * P.gi_rays; ++k)
+                                        (void)rng.next();
+                                    f.i = int(P.gi_rays) - 1; // as if the last bounce ray had just returned black
+                                    c = mk(0.0f, 0.0f, 0.0f);
+                                    ++depth, act = 2;
+                                } else {
+                                    ray = Ray{ s.P + s.n * P.diffuse_reflection_bias, gi_direction(ray.d, s.n, rng) };
+                                    ++depth, act = 1;
+                                }
+                            } else if (SHADOWS && P.shadows && S.n_lights > 0) {
+                                f.kind = kDirectShadow, f.i = 0;
+                                f.a = mk(0.0f, 0.0f, 0.0f), f.b = s.P, f.c = s.n, f.g = albedo;
+                                ray = Ray{ s.P + s.n * P.shadow_bias, light_term(S, 0, s.P, s.n).dir };
+                                act = 3;
+                            } else {
+                                c = add_direct_light(S, mk(0.0f, 0.0f, 0.0f), s, albedo, no_shadow) / gi_div;
+                            }
+                        } else if (m.x == 1) { // Reflective
+                            const V3 albedo = sample_texture(S, m.y, s);
+                            if (!S.reflections_on) {
+                                c = albedo;
+                            } else {
+                                f.kind = kReflect, f.a = albedo;
+                                ray = Ray{ s.P + s.n * P.reflection_bias, reflect(ray.d, s.n) };
+                                ++depth, act = 1;
+                            }
+                        } else if (m.x == 2) { // Refractive
+                            if (!S.refractions_on) {
+                                c = mk(0.0f, 0.0f, 0.0f);
+                            } else {
+                                V3 n = s.n;
+                                float outside = 1.0f, inside = __int_as_float(m.z);
+                                if (dot(ray.d, n) > 0.0f) { // leaving the volume
+                                    n = -n;
+                                    const float tmp = outside;
+                                    outside = inside, inside = tmp;
+                                }
+                                V3 rd = ray.d;
+                                const bool refracted = refract(rd, n, outside, inside);
+                                f.kind = refracted ? kRefractWaitReflection : kRefractTir;
+                                f.f = fresnel_term(1.0f + dot(ray.d, n));
+                                f.b = s.P + (-n) * 1e-2f; // the refraction_bias argument is dropped by the reference (crt_ray.h:33)
+                                f.c = rd;
+                                ray = Ray{ s.P + n * P.reflection_bias, reflect(ray.d, n) };
+                                ++depth, act = 1;
+                            }
+                        } else { // Constant
+                            c = sample_texture(S, m.y, s);
+                        }
+                        continue;
+                    }
+                    // act == 2: return c to the callers (the frame stack is the recursion's return path)
+                    if (depth == base_depth) {
+                        if (SEEDED)
+                            b.col[b.P + seed_start + px] = make_float4(c.x, c.y, c.z, 0.0f);
+                        else
+                            write_pixel(S, rgb, rgb8, px, ply, c);
+                        ply = -1;
+                        break;
+                    }
+                    Frame &f = frames[depth - 1];
+                    if (f.kind == kReflect) {
+                        c = tint(f.a, c);
+                    } else if (f.kind == kRefractTir) {
+                        // reflection colour passes through
+                    } else if (f.kind == kRefractWaitReflection) {
+                        f.a = c;
+                        f.kind = kRefractWaitRefraction;
+                        ray = Ray{ f.b, f.c };
+                        act = 1; // evaluate the refraction ray at the same depth
+                        continue;
+                    } else if (f.kind == kRefractWaitRefraction) {
+                        c = f.a * f.f + c * (1.0f - f.f);
+                    } else { // kDiffuseGi
+                        f.a = f.a + c;
+                        if (uint32_t(++f.i) < P.gi_rays) {
+                            ray = Ray{ f.b + f.c * P.diffuse_reflection_bias, gi_direction(f.e, f.c, rng) };
+                            act = 1;
+                            continue;
+                        }
+                        if (SHADOWS && P.shadows && S.n_lights > 0) { // the light loop of this surface, one shadow query per light
+                            f.kind = kDirectShadow, f.i = 0; // a (GI sum so far), b, c, g stay
+                            --depth;
+                            ray = Ray{ f.b + f.c * P.shadow_bias, light_term(S, 0, f.b, f.c).dir };
+                            act = 3;
+                            continue;
+                        }
+                        Surface s{};
+                        s.P = f.b, s.n = f.c;
+                        c = add_direct_light(S, f.a, s, f.g, no_shadow) / gi_div;
+                    }
+                    --depth;
+                }
+            }
+            __syncwarp();
+        }
+    }
+    if (STATS)
+        flush_counters(cn, counters);
+}
+
+} // namespace crtdev

@@ -1,0 +1,280 @@
+// TRACE stage, round 2: k_wf_trace_light's organisation (persistent warps, lane-level ray replacement, leaves parked
+// in two register slots and tested warp-wide, work stealing at the end of a level) around the LEAN walker of
+// crt_walk_lean.h.  Included by crt_wavefront.cuh after crt_trace_light.cuh.
+//
+// What changed against k_wf_trace_light and why (ncu r1zz: 138 SASS instructions per node visit at 77-79 % issue-slot
+// utilisation, 19 of 32 lanes active -- the kernel is bound by the instructions of a visit):
+//   * the visit itself: crt_walk_lean.h (direction-sign child order, sentinel stack entry, NaN-driven in-plane case);
+//   * pruning is ONE comparison per visit, tmin > best + slack with the threshold computed once per round; the
+//     wide-margin "everything pending is pruned" test runs only for lanes that were pruned;
+//   * a subtree a helper lane took over is replaced in the victim's stack by the scene's EMPTY LEAF (a real node the
+//     upload appends to the walk tree), so a visit never asks whether its node was stolen;
+//   * node visits are counted where the node is loaded (STATS builds).
+#pragma once
+
+#include "crt_walk_lean.h"
+
+namespace crtdev {
+
+#ifndef CRT_N_STEPS
+#define CRT_N_STEPS 8
+#endif
+#ifndef CRT_N_TRIGGER
+#define CRT_N_TRIGGER 16
+#endif
+#ifndef CRT_N_WAITERS
+#define CRT_N_WAITERS 6
+#endif
+#ifndef CRT_N_MINBLOCKS
+#define CRT_N_MINBLOCKS 10
+#endif
+#ifndef CRT_N_REFILL
+#define CRT_N_REFILL 25
+#endif
+
+static_assert(crtwalk::kWin == kWin, "stack window of the lean walker and of LightWarpShared");
+
+__device__ __forceinline__ crtwalk::Node as_walk_node(const int4 n) { return crtwalk::Node{ n.x, n.y, n.z, n.w }; }
+
+// ---- pieces shared with k_render_persistent -----------------------------------------------------------------------
+
+// idle lanes take over the bottom stack entries (the farthest pending subtrees) of lanes that still walk; see
+// k_wf_trace_light for the protocol.  `busy_lane` = this lane owns a ray or helps one; returns through the references.
+template <bool STATS>
+__device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWalker &w, unsigned lane, unsigned lt_mask, bool owns_work, bool &helper,
+                                           unsigned &src, int &stolen, uint32_t empty_leaf, Counters &cn) {
+    const unsigned full = 0xffffffffu;
+    const bool thief = !owns_work && !helper;
+    const unsigned thieves = __ballot_sync(full, thief);
+    stolen = max(1, min(stolen, w.sp)); // entries in [1, stolen) are tombstones; popping past them frees the slots
+    const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
+    const bool can_give = (owns_work || helper) && !w.done() && w.node >= 0 && w.lo == 0 && w.sp - stolen >= 2 && (lowest & crtwalk::kFlagBit) == 0u &&
+                          lowest != empty_leaf;
+    const unsigned victims = __ballot_sync(full, can_give);
+    if (thieves != 0u && victims != 0u) {
+        const int pairs = min(__popc(thieves), __popc(victims));
+        const int rank = thief ? __popc(thieves & lt_mask) : (can_give ? __popc(victims & lt_mask) : 32);
+        const bool paired = rank < pairs;
+        const unsigned v = (paired && thief) ? __fns(victims, 0, rank + 1) : lane; // the rank-th victim
+        const unsigned v_src = __shfl_sync(full, src, v);
+        const int v_stolen = __shfl_sync(full, stolen, v);
+        if (paired && thief) {
+            const uint2 e = ws.stack[v_stolen & (kWin - 1)][v];
+            // exit distance of that entry = entry distance of the one below it (tombstones and the sentinel keep theirs)
+            const float exit_t = __uint_as_float(ws.stack[(v_stolen - 1) & (kWin - 1)][v].y);
+            helper = true;
+            src = v_src;
+            stolen = 1;
+            w.begin(ws, lane, int(e.x), __uint_as_float(e.y), exit_t);
+            atomicAdd(&ws.helpers[v_src], 1);
+        }
+        __syncwarp();
+        if (paired && !thief) {
+            ws.stack[stolen & (kWin - 1)][lane].x = empty_leaf;
+            ++stolen;
+        }
+        __syncwarp();
+    }
+}
+
+// up to STEPS node visits of this lane's walk; a reached leaf is parked in a free slot and the walk goes on
+// (speculatively: its triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong).
+// Returns true when the lane is blocked on a leaf with both slots taken.
+template <bool STATS, int STEPS>
+__device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, crtwalk::LeanWalker &w, uint2 *spill, unsigned lane, unsigned src,
+                                          int &p0_first, int &p0_count, int &p1_first, int &p1_count, Counters &cn) {
+    const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
+    const float threshold = crtwalk::prune_threshold(best_t);
+#pragma unroll
+    for (int k = 0; k < STEPS; ++k) {
+        if (w.done())
+            break;
+        if (w.tmin > threshold) { // this subtree starts beyond the best hit
+            if (w.pruned_everything(best_t))
+                break;
+        } else {
+            const int4 n = kd_node_at(S, w.node);
+            if (STATS)
+                ++cn.node_tests;
+            if (n.w != 3) {
+                w.step(ws, spill, lane, src, as_walk_node(n));
+                if (w.node >= 0)
+                    continue;
+            } else if (p0_count == 0) {
+                p0_first = n.y, p0_count = n.z;
+            } else if (p1_count == 0) {
+                p1_first = n.y, p1_count = n.z;
+            } else {
+                return true; // both slots taken: wait for the test phase
+            }
+        }
+        w.pop(ws, spill, lane);
+    }
+    return false;
+}
+
+// test phase: every parked leaf of every lane at once.  shfl prefix sum of the parked counts, owner lane by binary
+// search, every lane tests whichever (ray, triangle) pair comes next; hits merge through a 64-bit atomicMin on
+// (t bits, triangle) = the reference's winner rule (closest, ties to the lowest parse index).
+template <bool STATS>
+__device__ __forceinline__ void lean_test_parked(const DScene &S, LightWarpShared &ws, unsigned lane, unsigned src, int p0_first, int p0_count, int p1_first,
+                                                 int p1_count, Counters &cn) {
+    const unsigned full = 0xffffffffu;
+    const int mine = p0_count + p1_count;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(full, incl, o);
+        if (int(lane) >= o)
+            incl += v;
+    }
+    const int items = __shfl_sync(full, incl, 31);
+    const int excl = incl - mine;
+    for (int base_item = 0; base_item < items; base_item += 32) {
+        const int item = base_item + int(lane);
+        // owner = last lane whose exclusive prefix is <= item; lanes with equal prefixes have nothing parked except the
+        // last of the run, which owns the item
+        int owner = 0;
+#pragma unroll
+        for (int stride = 16; stride > 0; stride >>= 1) {
+            const int probe = __shfl_sync(full, excl, owner + stride);
+            if (probe <= item)
+                owner += stride;
+        }
+        const int o_excl = __shfl_sync(full, excl, owner);
+        const int o_first0 = __shfl_sync(full, p0_first, owner), o_count0 = __shfl_sync(full, p0_count, owner);
+        const int o_first1 = __shfl_sync(full, p1_first, owner);
+        owner = int(__shfl_sync(full, src, owner)); // a helper's leaves are tested against the ray it helps
+        if (item < items) {
+            const int k = item - o_excl;
+            const uint32_t ref = __ldg(&S.kd_refs[k < o_count0 ? o_first0 + k : o_first1 + (k - o_count0)]);
+            const int tri = int(ref & 0x7FFFFFFFu);
+            const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
+            const V3 o = mk(ws.ray[0][owner], ws.ray[1][owner], ws.ray[2][owner]), d = mk(ws.ray[3][owner], ws.ray[4][owner], ws.ray[5][owner]);
+            if (STATS)
+                ++cn.tri_tests;
+            float t;
+            if (triangle_test_flat(A, B, C, (ref >> 31) != 0, o, d, t)) {
+                t = t + 0.0f; // -0 -> +0 so the bit pattern orders like the value
+                atomicMin(&ws.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)uint32_t(tri));
+            }
+        }
+    }
+    __syncwarp();
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+
+template <bool STATS>
+__global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
+                                                                                const __grid_constant__ WfBuffers b, int level,
+                                                                                Counters *__restrict__ counters) {
+    WfCtl *ctl = b.ctl;
+    const int start = level == 0 ? 0 : level_start(ctl, level);
+    const int total = level == 0 ? ctl->count[0] : level_count(ctl, b.cap, level, start);
+    Counters cn{};
+    __shared__ LightWarpShared shared[kTraceWarps];
+    LightWarpShared &ws = shared[threadIdx.x >> 5];
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned full = 0xffffffffu;
+    const uint32_t empty_leaf = uint32_t(S.kd_empty_leaf);
+    crtwalk::LeanWalker w;
+    uint2 spill[kStack]; // stack entries below the shared-memory window
+    w.node = crtwalk::kDone, w.sp = 1, w.lo = 0, w.flagged = 0, w.tmin = 0.0f, w.tmax = 0.0f;
+    int my = -1;      // index of my ray within the level, -1 = idle
+    int node_id = 0;  // where my ray's hit record goes
+    bool live = false;
+    int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0; // parked leaves
+    bool exhausted = false;
+    unsigned src = lane;  // lane whose ray I am walking: myself, or the owner of the subtree I took over
+    bool helper = false;  // I own no ray, I walk a stolen subtree of lane `src`'s ray
+    int stolen = 1;       // entries [1, stolen) of my stack are tombstones (helpers took them over)
+    for (;;) {
+        // ---- refill idle lanes from the level's queue
+        const unsigned busy = __ballot_sync(full, my >= 0 || helper);
+        if (!exhausted && __popc(busy) < CRT_N_REFILL) {
+            const unsigned idle = ~busy;
+            int base = 0;
+            if (lane == 0)
+                base = atomicAdd(&ctl->fetch[level], __popc(idle));
+            base = __shfl_sync(full, base, 0);
+            if (base + __popc(idle) >= total)
+                exhausted = true;
+            if (my < 0 && !helper) {
+                const int i = base + __popc(idle & lt_mask);
+                if (i < total) {
+                    V3 o, d, inv;
+                    float t_enter, t_exit;
+                    if (level == 0) {
+                        const float4 rd = b.ray0_d[i], ri = b.ray0_i[i];
+                        node_id = b.ray0_slot[i];
+                        o = mk(S.cam.position[0], S.cam.position[1], S.cam.position[2]);
+                        d = xyz(rd), inv = xyz(ri), t_enter = rd.w, t_exit = ri.w;
+                    } else {
+                        const float4 ro = b.ray_o[start + i], rd = b.ray_d[start + i], ri = b.ray_i[start + i];
+                        node_id = b.P + start + i;
+                        o = xyz(ro), d = xyz(rd), inv = xyz(ri), t_enter = ro.w, t_exit = rd.w;
+                        if (STATS) {
+                            ++cn.rays;
+                            ++cn.rays_by_depth[level];
+                            ++cn.node_tests;
+                        }
+                    }
+                    my = i;
+                    src = lane;
+                    stolen = 1;
+                    ws.helpers[lane] = 0;
+                    live = t_enter <= t_exit;
+                    w.node = crtwalk::kDone;
+                    if (live) {
+                        w.start(ws, lane, o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_enter, t_exit);
+                        ws.best[lane] = kNoHitKey;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        if (__ballot_sync(full, my >= 0 || helper) == 0u) {
+            if (exhausted)
+                break;
+            continue;
+        }
+        if (exhausted)
+            lean_steal<STATS>(ws, w, lane, lt_mask, my >= 0, helper, src, stolen, empty_leaf, cn);
+        // ---- walk
+        bool blocked = false;
+        if ((my >= 0 || helper) && !w.done())
+            blocked = lean_walk<STATS, CRT_N_STEPS>(S, ws, w, spill, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
+        // ---- test phase: all parked leaves of all lanes at once
+        const unsigned parked = __ballot_sync(full, p0_count > 0);
+        const unsigned walkers = __ballot_sync(full, (my >= 0 || helper) && !w.done() && !blocked);
+        const unsigned waiting = __ballot_sync(full, (my >= 0 || helper) && w.done() && p0_count > 0);
+        const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_N_WAITERS);
+        if (fire) {
+            lean_test_parked<STATS>(S, ws, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
+            p0_count = 0, p1_count = 0;
+        }
+        // ---- retire: walk over and nothing parked; helpers first, then the rays nobody is helping any more
+        if (helper && w.done() && p0_count == 0) {
+            atomicSub(&ws.helpers[src], 1);
+            helper = false;
+            src = lane;
+        }
+        __syncwarp();
+        if (my >= 0 && w.done() && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0)) {
+            Hit h{ kInf, -1 };
+            if (live) {
+                const unsigned long long key = ws.best[lane];
+                h.t = __uint_as_float(unsigned(key >> 32));
+                h.tri = int(unsigned(key & 0xffffffffull));
+            }
+            b.hit[node_id] = make_float2(h.t, __int_as_float(h.tri));
+            my = -1;
+        }
+    }
+    if (STATS)
+        flush_counters(cn, counters);
+}
+
+} // namespace crtdev

@@ -52,6 +52,7 @@ struct WavefrontState {
     int sm_count = 0;
     int *h_flags = nullptr;   // pinned: {overflow, pend_hi, pend_lo_inv}
     double grow = 1.0;        // pool = grow * pixels
+    bool classic_walker = false; // $CRT_WALKER=classic
 };
 
 enum NodeKind : int { kTerminal = 0, kNodeReflect = 1, kNodeRefract = 2, kNodeTir = 3 };
@@ -141,6 +142,7 @@ __device__ __forceinline__ void write_ray(const DScene &S, const WfBuffers &b, i
 } // namespace crtdev
 #include "crt_trace.cuh"
 #include "crt_trace_light.cuh"
+#include "crt_trace_lean.cuh"
 #include "crt_trace_packet.cuh"
 namespace crtdev {
 
@@ -412,10 +414,15 @@ template <int TRAV>
 inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, const DParams &dp, bool stats, int level, int blocks, Counters *counters,
                                    cudaStream_t stream, bool light) {
     if (TRAV == CRT_TRAVERSAL_KD && light) {
-        if (stats)
-            k_wf_trace_light<true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+        if (w.classic_walker) { // $CRT_WALKER=classic: round 1's k_wf_trace_light, kept for A/B measurements
+            if (stats)
+                k_wf_trace_light<true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+            else
+                k_wf_trace_light<false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+        } else if (stats)
+            k_wf_trace_lean<true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
         else
-            k_wf_trace_light<false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
+            k_wf_trace_lean<false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
         return;
     }
     if (stats)
@@ -442,7 +449,7 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     // evaluates the subtrees of the queued level-L rays (k_render_persistent<SEEDED>) and runs the resolves of levels L-1 .. 0
     const int all_levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
     const int levels = first_levels_only > 0 ? min(first_levels_only, all_levels) : all_levels;
-    const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? CRT_L_MINBLOCKS : 8);
+    const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? (w.classic_walker ? CRT_L_MINBLOCKS : CRT_N_MINBLOCKS) : 8);
     int n = 0;
     // primary level of the k-d walk as warp packets (crt_trace_packet.cuh): ray generation, root-box entry and the walk
     // of a whole 8x4 patch in one kernel, no ray records
