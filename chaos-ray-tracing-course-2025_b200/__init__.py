@@ -93,12 +93,12 @@ class RenderParams(C.Structure):
 class RenderStats(C.Structure):
     _fields_ = [("gpu_ms", C.c_float), ("kernel_launches", C.c_int32), ("rows_rendered", C.c_int32), ("pad", C.c_int32),
                 ("rays", C.c_uint64), ("rays_by_depth", C.c_uint64 * 16), ("shadow_rays", C.c_uint64),
-                ("node_tests", C.c_uint64), ("tri_tests", C.c_uint64)]
+                ("node_tests", C.c_uint64), ("tri_tests", C.c_uint64), ("entered_rays", C.c_uint64)]
 
     def as_dict(self):
         return {"gpu_ms": self.gpu_ms, "kernel_launches": self.kernel_launches, "rows_rendered": self.rows_rendered,
                 "rays": self.rays, "rays_by_depth": list(self.rays_by_depth), "shadow_rays": self.shadow_rays,
-                "node_tests": self.node_tests, "tri_tests": self.tri_tests}
+                "node_tests": self.node_tests, "tri_tests": self.tri_tests, "entered_rays": self.entered_rays}
 
 
 def _load_library():

@@ -151,6 +151,7 @@ void fill_stats(const crt_cuda_ctx *ctx, crt_render_stats *stats, float ms) {
         stats->shadow_rays = c.shadow_rays;
         stats->node_tests = c.node_tests;
         stats->tri_tests = c.tri_tests;
+        stats->entered_rays = c.entered;
         for (int i = 0; i < 16; ++i)
             stats->rays_by_depth[i] = c.rays_by_depth[i];
     }
@@ -574,6 +575,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)
     if (const char *k = std::getenv("CRT_PACKET"); k && *k)
         ctx->packet_mode = *k == '1' ? 1 : 0;
+    ctx->wf.grow = 1.0; // the ray pool is re-sized per scene (it only grows while one scene is rendered)
     ctx->have_scene = true;
     return CRT_OK;
 }
@@ -606,12 +608,23 @@ int crt_cuda_synchronize(crt_cuda_ctx *ctx, crt_render_stats *stats) {
         return CRT_ERR_INVALID;
     CRT_CK(ctx, cudaSetDevice(ctx->device));
     CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
-    // a bounce level outgrew the ray pool: grow it and render the frame again (rare; the pool then stays large)
+    // A bounce level outgrew the ray pool: size the pool from what the discarded frame counted and render the frame
+    // again (rare; the pool then stays large until the next scene upload).  The counts of an overflowed frame are a lower
+    // bound -- rays that found no room spawned no children -- so this may take a few rounds: at least double every time,
+    // and at least 1.25 x the counted demand.  A frame that still does not fit is an ERROR, never a silently black or
+    // stale frame (a pool of P * (2^(d+1) - 2) rays always fits; cudaMalloc fails first for deep glass at large sizes).
     ctx->rerendered = false;
-    for (int attempt = 0; ctx->last_wavefront && ctx->wf.h_flags && *ctx->wf.h_flags && attempt < 6; ++attempt) {
-        ctx->rerendered = true;
+    constexpr int kPoolAttempts = 12;
+    for (int attempt = 0; ctx->last_wavefront && ctx->wf.h_flags && *ctx->wf.h_flags; ++attempt) {
         *ctx->wf.h_flags = 0;
-        ctx->wf.grow *= 2.0;
+        if (attempt == kPoolAttempts)
+            return fail(ctx, CRT_ERR_CUDA, "the wavefront ray pool still overflows after 12 re-sized attempts; the frame was NOT rendered");
+        ctx->rerendered = true;
+        double demand = 0.0;
+        for (int l = 1; l < kMaxLevels; ++l)
+            demand += double(ctx->wf.h_count[l]);
+        const double pixels = double(std::max(1, ctx->wf.b.P));
+        ctx->wf.grow = std::max(ctx->wf.grow * 2.0, 1.25 * demand / pixels);
         const crt_render_params again = ctx->last_params;
         if (int rc = enqueue_frame(ctx, &again))
             return rc;
@@ -968,14 +981,17 @@ int crt_cuda_group_render(crt_cuda_group *g, const crt_render_params *params, fl
         }
         return CRT_OK;
     };
-    // enqueue everything on every device first (the devices then work concurrently), complete afterwards
+    // enqueue the kernels on every device first, so that all of them are working before any copy is issued: a
+    // device-to-host copy into PAGEABLE memory (crt::render_image passes a std::vector) blocks the calling thread until
+    // that device is done, which would serialise the devices if it sat in the loop that launches them
     for (int i = 0; i < n; ++i) {
         crt_cuda_ctx *ctx = g->ranks[i];
         crt_render_params p = *params;
         p.rank = i, p.world = n, p.band_rows = band;
         CRT_GROUP_CK(ctx, enqueue_frame(ctx, &p));
-        CRT_GROUP_CK(ctx, issue_outputs(ctx, i));
     }
+    for (int i = 0; i < n; ++i)
+        CRT_GROUP_CK(g->ranks[i], issue_outputs(g->ranks[i], i));
     crt_render_stats total{};
     for (int i = 0; i < n; ++i) {
         crt_render_stats st{};

@@ -80,6 +80,7 @@ struct DParams {
 struct Counters {
     unsigned long long rays, shadow_rays, node_tests, tri_tests;
     unsigned long long rays_by_depth[16];
+    unsigned long long entered; // rays that enter the root box (the rays a walk is started for); the others end in ray setup
 };
 
 constexpr int kStack = 48; // tree depth <= 40 (leaf rule depth > 39), stack need <= depth + 2; checked at upload
@@ -227,6 +228,8 @@ __device__ __forceinline__ Hit trace_literal(const DScene &S, const Ray &r, Coun
     int stack[kStack];
     int sp = 0;
     stack[sp++] = 0;
+    if (STATS)
+        ++cn->entered; // the reference-order traversal has no entry test: every ray starts at the root node
     while (sp > 0) {
         const int node = stack[--sp];
         const float4 lo = __ldg(&S.box_nodes[2 * node]), hi = __ldg(&S.box_nodes[2 * node + 1]);
@@ -527,6 +530,8 @@ template <bool STATS>
 __device__ __forceinline__ Hit trace_kd(const DScene &S, const Ray &r, Counters *cn, int *mailbox = nullptr, int mailbox_stride = 0) {
     KdWalker w;
     if (w.init<STATS>(S, r, cn)) {
+        if (STATS)
+            ++cn->entered;
         mailbox_clear(mailbox, mailbox_stride);
         while (!w.done())
             w.advance<STATS>(S, cn, mailbox, mailbox_stride);

@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     Pcg32 rng{};
     Frame frames[kMaxDepthCap + 1];
     // ---- walk state (see k_wf_trace_light)
-    int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0;
+    int parked0 = -1, parked1 = -1; // parked leaves (node ids)
     bool exhausted = false;
     unsigned src = lane;
     bool helper = false;
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                     src = lane, stolen = 1;
                     ws.helpers[lane] = 0;
                     w.node = crtwalk::kDone;
-                    p0_count = 0, p1_count = 0;
+                    parked0 = -1, parked1 = -1;
                 }
             }
             __syncwarp();
@@ -154,25 +154,25 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         // ---- walk: a few node visits per lane; a leaf is parked and the walk goes on (crt_trace_lean.cuh: lean_walk)
         bool blocked = false;
         if ((ply >= 0 || helper) && !w.done()) // fresh pixels have a finished walk
-            blocked = lean_walk<STATS, (GI ? CRT_P_STEPS_GI : CRT_P_STEPS)>(S, ws, w, spill, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
+            blocked = lean_walk<STATS, (GI ? CRT_P_STEPS_GI : CRT_P_STEPS)>(S, ws, w, spill, lane, src, parked0, parked1, cn);
         // ---- test phase: all parked leaves of all lanes at once
-        const unsigned parked = __ballot_sync(full, p0_count > 0);
+        const unsigned parked = __ballot_sync(full, parked0 >= 0);
         const unsigned walkers = __ballot_sync(full, (ply >= 0 || helper) && !w.done() && !blocked);
-        const unsigned waiting = __ballot_sync(full, (ply >= 0 || helper) && w.done() && p0_count > 0);
+        const unsigned waiting = __ballot_sync(full, (ply >= 0 || helper) && w.done() && parked0 >= 0);
         const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_N_WAITERS);
         if (fire) {
-            lean_test_parked<STATS>(S, ws, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
-            p0_count = 0, p1_count = 0;
+            lean_test_parked<STATS>(S, ws, lane, src, parked0, parked1, cn);
+            parked0 = -1, parked1 = -1;
         }
         // ---- helpers that finished hand their subtree's result back (it is already merged into the owner's best)
-        if (helper && w.done() && p0_count == 0) {
+        if (helper && w.done() && parked0 < 0) {
             atomicSub(&ws.helpers[src], 1);
             helper = false;
             src = lane;
         }
         __syncwarp();
         // ---- SHADE phase: lanes whose query is finished (or whose pixel is new) continue their pixel's recursion
-        const bool ready = ply >= 0 && w.done() && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
+        const bool ready = ply >= 0 && w.done() && parked0 < 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
         const unsigned ready_m = __ballot_sync(full, ready);
         const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && !w.done());
         patience = ready_m != 0u ? patience + 1 : 0;
@@ -208,6 +208,8 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                             ++cn.node_tests;
                         }
                         const RaySetup q = ray_setup(S, ray);
+                        if (STATS && q.live)
+                            ++cn.entered;
                         if (q.live) { // leave the phase: the walk answers this query
                             w.start(ws, lane, ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, q.inv.x, q.inv.y, q.inv.z, q.tmin, q.tmax);
                             ws.best[lane] = kNoHitKey;

@@ -289,7 +289,7 @@ __device__ __forceinline__ void trace_level_literal(const DScene &S, const DPara
             ++cn.rays;
             ++cn.rays_by_depth[level];
         }
-        const Hit h = trace_literal<STATS>(S, r, &cn);
+        const Hit h = trace_literal<STATS>(S, r, &cn); // counts the ray as entered
         b.hit[level == 0 ? i : b.P + start + i] = make_float2(h.t, __int_as_float(h.tri));
     }
 }
@@ -361,6 +361,8 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_MINBLOCKS) k_wf_trace(const _
                     my = i;
                     my_mark = tested;
                     live = t_enter <= t_exit;
+                    if (STATS && level > 0 && live)
+                        ++cn.entered; // (level 0: counted by the ray generation)
                     w.node = -1;
                     if (live) {
                         w.start(ws, lane, o, d, inv, t_enter, t_exit);

@@ -59,13 +59,13 @@ __device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWal
         const unsigned v_src = __shfl_sync(full, src, v);
         const int v_stolen = __shfl_sync(full, stolen, v);
         if (paired && thief) {
+            // the victim's lowest live entry {node, exit}; its interval starts where the entry above it ends
             const uint2 e = ws.stack[v_stolen & (kWin - 1)][v];
-            // exit distance of that entry = entry distance of the one below it (tombstones and the sentinel keep theirs)
-            const float exit_t = __uint_as_float(ws.stack[(v_stolen - 1) & (kWin - 1)][v].y);
+            const float enter_t = __uint_as_float(ws.stack[(v_stolen + 1) & (kWin - 1)][v].y);
             helper = true;
             src = v_src;
             stolen = 1;
-            w.begin(ws, lane, int(e.x), __uint_as_float(e.y), exit_t);
+            w.begin(ws, lane, int(e.x), enter_t, __uint_as_float(e.y));
             atomicAdd(&ws.helpers[v_src], 1);
         }
         __syncwarp();
@@ -77,49 +77,55 @@ __device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWal
     }
 }
 
-// up to STEPS node visits of this lane's walk; a reached leaf is parked in a free slot and the walk goes on
-// (speculatively: its triangles have not been tested yet, so the distance used for pruning may be stale -- never wrong).
-// Returns true when the lane is blocked on a leaf with both slots taken.
+// up to STEPS node visits of this lane's walk; a reached leaf is PARKED (its node id kept in one of two registers) and
+// the walk goes on -- speculatively: its triangles have not been tested yet, so the distance used for pruning may be
+// stale, never wrong.  Returns true when the lane is blocked on a leaf with both slots taken.
 template <bool STATS, int STEPS>
 __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, crtwalk::LeanWalker &w, uint2 *spill, unsigned lane, unsigned src,
-                                          int &p0_first, int &p0_count, int &p1_first, int &p1_count, Counters &cn) {
+                                          int &parked0, int &parked1, Counters &cn) {
     const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
     const float threshold = crtwalk::prune_threshold(best_t);
+    bool stopped = false;
 #pragma unroll
     for (int k = 0; k < STEPS; ++k) {
-        if (w.done())
+        if (w.done() | stopped)
             break;
-        if (w.tmin > threshold) { // this subtree starts beyond the best hit
-            if (w.pruned_everything(best_t))
-                break;
-        } else {
-            const int4 n = kd_node_at(S, w.node);
+        const int at = w.node;
+        int4 n = make_int4(0, 0, 0, 0);
+        if (!(w.tmin > threshold)) { // (a predicated load: a pruned subtree's node is never fetched)
+            n = kd_node_at(S, at);
             if (STATS)
                 ++cn.node_tests;
-            if (n.w != 3) {
-                w.step(ws, spill, lane, src, as_walk_node(n));
-                if (w.node >= 0)
-                    continue;
-            } else if (p0_count == 0) {
-                p0_first = n.y, p0_count = n.z;
-            } else if (p1_count == 0) {
-                p1_first = n.y, p1_count = n.z;
-            } else {
-                return true; // both slots taken: wait for the test phase
-            }
         }
-        w.pop(ws, spill, lane);
+        bool took_leaf;
+        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf);
+        const bool park = took_leaf & (n.z > 0); // (a leaf without triangles is over at once)
+        const bool to0 = park & (parked0 < 0), to1 = park & (parked0 >= 0);
+        parked0 = to0 ? at : parked0;
+        parked1 = to1 ? at : parked1;
     }
-    return false;
+    if (!stopped)
+        return false;
+    w.make_room(ws, spill, lane); // (rare: stack window full / popped entry spilled; nothing to do for a blocked leaf)
+    return !w.done() && parked1 >= 0; // blocked: both slots taken -- the test phase must run before this lane walks on
 }
 
 // test phase: every parked leaf of every lane at once.  shfl prefix sum of the parked counts, owner lane by binary
 // search, every lane tests whichever (ray, triangle) pair comes next; hits merge through a 64-bit atomicMin on
 // (t bits, triangle) = the reference's winner rule (closest, ties to the lowest parse index).
 template <bool STATS>
-__device__ __forceinline__ void lean_test_parked(const DScene &S, LightWarpShared &ws, unsigned lane, unsigned src, int p0_first, int p0_count, int p1_first,
-                                                 int p1_count, Counters &cn) {
+__device__ __forceinline__ void lean_test_parked(const DScene &S, LightWarpShared &ws, unsigned lane, unsigned src, int parked0, int parked1, Counters &cn) {
     const unsigned full = 0xffffffffu;
+    // the parked leaves' records again (they were loaded a few visits ago: L1)
+    int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0;
+    if (parked0 >= 0) {
+        const int4 n = kd_node_at(S, parked0);
+        p0_first = n.y, p0_count = n.z;
+    }
+    if (parked1 >= 0) {
+        const int4 n = kd_node_at(S, parked1);
+        p1_first = n.y, p1_count = n.z;
+    }
     const int mine = p0_count + p1_count;
     int incl = mine;
 #pragma unroll
@@ -185,7 +191,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
     int my = -1;      // index of my ray within the level, -1 = idle
     int node_id = 0;  // where my ray's hit record goes
     bool live = false;
-    int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0; // parked leaves
+    int parked0 = -1, parked1 = -1; // parked leaves (node ids)
     bool exhausted = false;
     unsigned src = lane;  // lane whose ray I am walking: myself, or the owner of the subtree I took over
     bool helper = false;  // I own no ray, I walk a stolen subtree of lane `src`'s ray
@@ -226,6 +232,8 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
                     stolen = 1;
                     ws.helpers[lane] = 0;
                     live = t_enter <= t_exit;
+                    if (STATS && level > 0 && live)
+                        ++cn.entered; // (level 0: counted by the ray generation)
                     w.node = crtwalk::kDone;
                     if (live) {
                         w.start(ws, lane, o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_enter, t_exit);
@@ -245,24 +253,24 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
         // ---- walk
         bool blocked = false;
         if ((my >= 0 || helper) && !w.done())
-            blocked = lean_walk<STATS, CRT_N_STEPS>(S, ws, w, spill, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
+            blocked = lean_walk<STATS, CRT_N_STEPS>(S, ws, w, spill, lane, src, parked0, parked1, cn);
         // ---- test phase: all parked leaves of all lanes at once
-        const unsigned parked = __ballot_sync(full, p0_count > 0);
+        const unsigned parked = __ballot_sync(full, parked0 >= 0);
         const unsigned walkers = __ballot_sync(full, (my >= 0 || helper) && !w.done() && !blocked);
-        const unsigned waiting = __ballot_sync(full, (my >= 0 || helper) && w.done() && p0_count > 0);
+        const unsigned waiting = __ballot_sync(full, (my >= 0 || helper) && w.done() && parked0 >= 0);
         const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_N_WAITERS);
         if (fire) {
-            lean_test_parked<STATS>(S, ws, lane, src, p0_first, p0_count, p1_first, p1_count, cn);
-            p0_count = 0, p1_count = 0;
+            lean_test_parked<STATS>(S, ws, lane, src, parked0, parked1, cn);
+            parked0 = -1, parked1 = -1;
         }
         // ---- retire: walk over and nothing parked; helpers first, then the rays nobody is helping any more
-        if (helper && w.done() && p0_count == 0) {
+        if (helper && w.done() && parked0 < 0) {
             atomicSub(&ws.helpers[src], 1);
             helper = false;
             src = lane;
         }
         __syncwarp();
-        if (my >= 0 && w.done() && p0_count == 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0)) {
+        if (my >= 0 && w.done() && parked0 < 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0)) {
             Hit h{ kInf, -1 };
             if (live) {
                 const unsigned long long key = ws.best[lane];

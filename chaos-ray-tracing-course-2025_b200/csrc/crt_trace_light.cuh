@@ -111,6 +111,8 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_L_MINBLOCKS) k_wf_trace_light
                     stolen = 0;
                     ws.helpers[lane] = 0;
                     live = t_enter <= t_exit;
+                    if (STATS && level > 0 && live)
+                        ++cn.entered; // (level 0: counted by the ray generation)
                     w.node = -1;
                     if (live) {
                         w.start(ws, lane, o, d, inv, t_enter, t_exit);

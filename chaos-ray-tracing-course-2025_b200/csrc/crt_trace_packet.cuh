@@ -51,6 +51,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
                 ++cn.rays;
                 ++cn.rays_by_depth[0];
                 ++cn.node_tests;
+                cn.entered += q.live ? 1 : 0;
             }
         }
         // a ray that misses the root box hits nothing: its pixel is final here; the others are queued for the level-0

@@ -15,8 +15,9 @@
 //     children TraceWalker visits, plus the far side when the origin lies on the plane itself;
 //   * no "absent child x near/far x both" case table: visit-first / visit-second are two comparisons, an absent child
 //     simply masks its side;
-//   * the stack holds a SENTINEL entry {kDone, root exit} at the bottom: pop never asks whether the stack is empty or
-//     whether the entry below exists;
+//   * stack entries hold {node, EXIT distance}; the entry distance of a popped subtree is the tmax the walk has at that
+//     moment, so a pop is ONE load (before: the entry and the one below it), and a SENTINEL entry {kDone, root exit} at
+//     the bottom means pop never asks whether the stack is empty;
 //   * a ray lying IN a split plane (tp = 0 * inf = NaN) takes both children with the whole interval through the NaN
 //     semantics of the comparisons and of fminf / fmaxf; only its stack entry needs the flag bit (rare path);
 //   * pruning against the best hit is one comparison per visit against best + slack, computed once per round.
@@ -43,8 +44,8 @@ constexpr int kWin = 8;                    // top-of-stack window per lane in sh
 struct Node {   // crt_kd_node as the kernels load it: {split bits, a, b, axis} / {0, first, count, 3}
     int32_t x, y, z, w;
 };
-struct Entry {  // {node | kFlagBit, entry distance bits}; the EXIT distance of an entry is the entry distance of the
-    uint32_t x, y; // entry below it (every push clips the current interval at the pushed plane)
+struct Entry {  // {node | kFlagBit, exit distance bits}
+    uint32_t x, y;
 };
 
 CRT_WALK_FN float bits_to_float(uint32_t u) {
@@ -71,9 +72,14 @@ CRT_WALK_FN float prune_threshold(float best_t) { return fmaf(fabsf(best_t), 1e-
 
 // WS: per-warp storage with  float ray[9][32]  (origin, direction, 1/direction)  and  Entry-like stack[kWin][32]
 // SPILL: Entry-like array of kStack entries owned by the caller (local memory on the device)
+//
+// Stack entry = {node | kFlagBit, EXIT distance of the pushed subtree}.  Its ENTRY distance need not be stored: when an
+// entry is popped, everything pushed after it has been popped too, so the current tmax is again what the push left
+// behind -- the plane distance the entry's interval starts at (or less, within the slack: a superset).  A pop is one
+// 8-byte load: tmin = tmax, tmax = entry.exit.
 struct LeanWalker {
     float tmin, tmax;
-    int node; // node to visit next; kDone when the walk is over; < 0 right after step() when the child is absent
+    int node; // node to visit next; kDone when the walk is over
     int sp, lo, flagged;
 
     CRT_WALK_FN bool done() const { return node == kDone; }
@@ -81,7 +87,7 @@ struct LeanWalker {
     template <class WS>
     CRT_WALK_FN void begin(WS &ws, unsigned lane, int first_node, float t_enter, float t_exit) {
         sp = 1, lo = 0, flagged = 0;
-        ws.stack[0][lane].x = uint32_t(kDone);
+        ws.stack[0][lane].x = uint32_t(kDone); // the sentinel: popping it ends the walk
         ws.stack[0][lane].y = float_to_bits(t_exit);
         tmin = t_enter, tmax = t_exit;
         node = first_node;
@@ -97,10 +103,23 @@ struct LeanWalker {
         ws.ray[6][lane] = ix, ws.ray[7][lane] = iy, ws.ray[8][lane] = iz;
     }
 
-    // ONE inner node `n` of the walk of lane `src`'s ray.  Leaves node = the child to visit next, or -1 when neither
-    // child is wanted (the caller pops).
-    template <class WS, class SPILL>
-    CRT_WALK_FN void step(WS &ws, SPILL *spill, unsigned lane, unsigned src, const Node n) {
+    // ONE iteration of the walk of lane `src`'s ray at node `n` (= the record of `node`; anything when the subtree is
+    // pruned), written as selects: the lanes of a warp sit at unrelated nodes and must share one instruction stream
+    // (ncu r2a: the same decisions written with branches ran at 14 instead of 19 active threads per instruction and
+    // issued as many warp instructions as the walker they replaced).  Returns true when the walk could NOT move on and
+    // the caller has something to do first: a leaf and no room for it (leaf_room was false), or one of the two rare
+    // events -- a push found the stack window full, a pop found its entry in the spill array -- which are not
+    // handled here (if-converted they would cost their issue slots on every visit): call make_room(), visit again.
+    // took_leaf: `n` is a leaf, the caller takes it, the walk has moved on.
+    //   threshold = prune_threshold (best_t): a subtree whose interval starts beyond it cannot beat or tie the best hit.
+    //   With a wide margin and no in-plane entry pending, everything on the stack is beyond it as well (exit distances
+    //   grow towards the bottom of the stack, and each interval starts where the one above it ends): the walk is over.
+    template <class WS>
+    CRT_WALK_FN bool visit(WS &ws, unsigned lane, unsigned src, const Node n, float threshold, float best_t, bool leaf_room, bool &took_leaf) {
+        const bool pruned = tmin > threshold;
+        const bool leaf = n.w == 3;
+        const bool inner = !pruned & !leaf;
+        // ---- the plane (a leaf's axis 3 reads direction.x and the word after the ray block: harmless, unused)
         const int axis = n.w;
         const float split = bits_to_float(uint32_t(n.x));
         const float oa = ws.ray[axis][src], ia = ws.ray[6 + axis][src];
@@ -111,52 +130,53 @@ struct LeanWalker {
         // that tp = -inf / +inf (direction parallel to the plane, origin off it) still means "behind" / "never
         // reached" -- a slack of inf would turn both comparisons into NaN tests -- and tp = NaN means both
         const bool want_first = !(fmaf(tp, 1.00001f, 1e-6f) < tmin), want_second = !(fmaf(tp, 0.99999f, -1e-6f) > tmax);
-        const bool go_first = want_first & (first >= 0), go_second = want_second & (second >= 0);
-        if (go_first & go_second) {
-            const bool in_plane = tp != tp;
-            if (sp - lo == kWin) { // window full (rare): the oldest entry goes to the spill array
-                spill[lo].x = ws.stack[lo & (kWin - 1)][lane].x, spill[lo].y = ws.stack[lo & (kWin - 1)][lane].y;
-                ++lo;
-            }
-            // an in-plane entry keeps the exit distance for the entries pushed above it and starts at 0 itself
+        const bool go_first = inner & want_first & (first >= 0), go_second = inner & want_second & (second >= 0);
+        // ---- rare events: nothing happens in this call
+        const bool full = go_first & go_second & (sp - lo == kWin);
+        const bool over = pruned & (flagged == 0) & (fmaf(tmin, 0.999f, -1e-4f) > best_t);
+        const bool wants_pop = (pruned & !over) | leaf | (inner & !go_first & !go_second);
+        const bool top_spilled = wants_pop & (sp - 1 < lo);
+        const bool frozen = full | top_spilled;
+        // ---- push the second child (a predicated store), go to the first
+        const bool push = go_first & go_second & !frozen;
+        const bool in_plane = tp != tp;
+        if (push) {
+            // an in-plane entry starts at 0 instead of at the current tmax (which the NaN leaves unclipped)
             ws.stack[sp & (kWin - 1)][lane].x = uint32_t(second) | (in_plane ? kFlagBit : 0u);
-            ws.stack[sp & (kWin - 1)][lane].y = float_to_bits(in_plane ? tmax : tp);
-            ++sp;
-            flagged += in_plane ? 1 : 0;
-            tmax = fminf(tmax, tp); // NaN: unchanged
+            ws.stack[sp & (kWin - 1)][lane].y = float_to_bits(tmax);
         }
-        tmin = (!go_first & go_second) ? fmaxf(tmin, tp) : tmin; // NaN: unchanged
-        node = go_first ? first : (go_second ? second : -1);
-    }
-
-    // next pending subtree; the sentinel at the bottom ends the walk
-    template <class WS, class SPILL>
-    CRT_WALK_FN void pop(const WS &ws, const SPILL *spill, unsigned lane) {
-        --sp;
-        uint32_t ex = ws.stack[sp & (kWin - 1)][lane].x, ey = ws.stack[sp & (kWin - 1)][lane].y;
-        uint32_t below = ws.stack[(sp - 1) & (kWin - 1)][lane].y;
-        if (sp <= lo) { // rare: the entry or the one below it was spilled (or this is the sentinel)
-            if (sp < lo)
-                ex = spill[sp].x, ey = spill[sp].y, lo = sp;
-            if (sp > 0)
-                below = sp - 1 >= lo ? ws.stack[(sp - 1) & (kWin - 1)][lane].y : spill[sp - 1].y;
-        }
-        const bool flag = (ex & kFlagBit) != 0u;
+        sp += push ? 1 : 0;
+        flagged += (push & in_plane) ? 1 : 0;
+        tmax = push ? fminf(tmax, tp) : tmax; // NaN: unchanged
+        const bool moved = (go_first | go_second) & !frozen;
+        tmin = (moved & !go_first) ? fmaxf(tmin, tp) : tmin; // NaN: unchanged
+        node = moved ? (go_first ? first : second) : node;
+        // ---- or hand the leaf over / pop the next pending subtree
+        const bool take_leaf = !pruned & leaf & leaf_room & !frozen, no_room = !pruned & leaf & !leaf_room;
+        const bool pop = wants_pop & !no_room & !frozen;
+        sp -= pop ? 1 : 0;
+        const uint32_t ex = ws.stack[sp & (kWin - 1)][lane].x, ey = ws.stack[sp & (kWin - 1)][lane].y;
+        const bool flag = pop & ((ex & kFlagBit) != 0u);
         flagged -= flag ? 1 : 0;
-        tmax = bits_to_float(below);
-        tmin = flag ? 0.0f : bits_to_float(ey);
-        node = int(ex & ~kFlagBit);
+        tmin = pop ? (flag ? 0.0f : tmax) : tmin;
+        tmax = pop ? bits_to_float(ey) : tmax;
+        node = pop ? int(ex & ~kFlagBit) : node;
+        node = over ? kDone : node;
+        took_leaf = take_leaf;
+        return no_room | frozen;
     }
 
-    // the node about to be visited starts beyond the best hit (tmin > threshold): with a wide margin and no in-plane
-    // entry pending, everything on the stack is beyond it as well (entry distances grow towards the bottom of the
-    // stack) and the walk is over; otherwise the caller pops
-    CRT_WALK_FN bool pruned_everything(float best_t) {
-        if (flagged == 0 && tmin - (fabsf(tmin) * 1e-3f + 1e-4f) > best_t) {
-            node = kDone;
-            return true;
+    // after visit() returned true: the oldest window entry goes to the spill array when the window is full, the top
+    // entry comes back from it when it is there (both are valid whenever their condition holds, whatever stopped the walk)
+    template <class WS, class SPILL>
+    CRT_WALK_FN void make_room(WS &ws, SPILL *spill, unsigned lane) {
+        if (sp - lo == kWin) {
+            spill[lo].x = ws.stack[lo & (kWin - 1)][lane].x, spill[lo].y = ws.stack[lo & (kWin - 1)][lane].y;
+            ++lo;
+        } else if (sp - 1 < lo && sp >= 1) {
+            lo = sp - 1;
+            ws.stack[lo & (kWin - 1)][lane].x = spill[lo].x, ws.stack[lo & (kWin - 1)][lane].y = spill[lo].y;
         }
-        return false;
     }
 };
 

@@ -50,7 +50,8 @@ struct WavefrontState {
     size_t ray0_capacity = 0; // allocated entries of ray0_*
     size_t pend_capacity = 0;
     int sm_count = 0;
-    int *h_flags = nullptr;   // pinned: {overflow, pend_hi, pend_lo_inv}
+    int *h_flags = nullptr;   // pinned: {overflow, pend_hi, pend_lo_inv} of the last frame ...
+    int *h_count = nullptr;   // ... and its rays per level (WfCtl::count): what a pool that overflowed is re-sized from
     double grow = 1.0;        // pool = grow * pixels
     bool classic_walker = false; // $CRT_WALKER=classic
 };
@@ -106,6 +107,7 @@ __global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constan
                 ++cn.rays;
                 ++cn.rays_by_depth[0];
                 ++cn.node_tests;
+                cn.entered += q.live ? 1 : 0;
             }
         }
         const unsigned live = __ballot_sync(0xffffffffu, q.live);
@@ -339,7 +341,9 @@ inline void wavefront_free(WavefrontState &w) {
     cudaFree(w.b.ray_o), cudaFree(w.b.ray_d), cudaFree(w.b.ray_i), cudaFree(w.b.ray0_d), cudaFree(w.b.ray0_i), cudaFree(w.b.ray0_slot), cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col), cudaFree(w.b.pend),
         cudaFree(w.b.ctl);
     cudaFreeHost(w.h_flags);
+    const bool classic = w.classic_walker;
     w = WavefrontState{};
+    w.classic_walker = classic;
 }
 
 inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
@@ -347,9 +351,10 @@ inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
     if (!w.b.ctl) {
         if ((e = cudaMalloc(&w.b.ctl, sizeof(WfCtl))) != cudaSuccess)
             return e;
-        if ((e = cudaHostAlloc(&w.h_flags, 3 * sizeof(int), cudaHostAllocDefault)) != cudaSuccess)
+        if ((e = cudaHostAlloc(&w.h_flags, (3 + kMaxLevels) * sizeof(int), cudaHostAllocDefault)) != cudaSuccess)
             return e;
-        w.h_flags[0] = w.h_flags[1] = w.h_flags[2] = 0;
+        w.h_count = w.h_flags + 3;
+        std::memset(w.h_flags, 0, (3 + kMaxLevels) * sizeof(int));
         cudaDeviceProp prop;
         int dev = 0;
         cudaGetDevice(&dev);
@@ -489,8 +494,13 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
         k_wf_resolve<<<w.sm_count * 4, 256, 0, stream>>>(S, dp, w.b, level, rgb, rgb8);
         ++n;
     }
-    if (secondary)
+    if (secondary) {
         e = cudaMemcpyAsync(w.h_flags, &w.b.ctl->overflow, 3 * sizeof(int), cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(w.h_count, w.b.ctl->count, kMaxLevels * sizeof(int), cudaMemcpyDeviceToHost, stream);
+    } else if (w.h_flags) {
+        w.h_flags[0] = 0; // a frame without secondary rays cannot overflow: never inherit an older frame's flag
+    }
     if (launches)
         *launches = n;
     return e != cudaSuccess ? e : cudaGetLastError();

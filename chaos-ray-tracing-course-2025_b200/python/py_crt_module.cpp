@@ -8,6 +8,7 @@
 //   _crt.DEFAULT_*                                                                     (:142-157)
 // Errors: ValueError("Invalid CRT Scene dict"), TypeError("Expected a RendererSettings instance"), and -- new --
 // RuntimeError when no CUDA device is usable (there is no CPU path to fall back to).
+#define PY_SSIZE_T_CLEAN // "y#" takes Py_ssize_t lengths
 #include <Python.h>
 #include <structseq.h>
 
@@ -142,15 +143,19 @@ PyObject *render_scene_from_dict_buffer(PyObject *, PyObject *args) {
     if (!render_from_args(args, image))
         return nullptr;
     const int W = image->width, H = image->height;
-    std::vector<float> rgba(size_t(W) * H * 4);
+    // the bytes object is filled in place: one pass over the frame, no intermediate copy
+    PyObject *bytes = PyBytes_FromStringAndSize(nullptr, Py_ssize_t(size_t(W) * size_t(H) * 4 * sizeof(float)));
+    if (!bytes)
+        return nullptr;
+    float *rgba = reinterpret_cast<float *>(PyBytes_AS_STRING(bytes));
     for (int y = 0; y < H; ++y) {
         const crt::Color *row = image->buffer.data() + size_t(y) * W;
-        float *dst = rgba.data() + size_t(H - y - 1) * W * 4;
+        float *dst = rgba + size_t(H - y - 1) * W * 4; // vertical flip, as the list (reference :102-116)
         for (int x = 0; x < W; ++x) {
             dst[4 * x] = row[x].x, dst[4 * x + 1] = row[x].y, dst[4 * x + 2] = row[x].z, dst[4 * x + 3] = 1.0f;
         }
     }
-    return Py_BuildValue("iiy#", W, H, reinterpret_cast<const char *>(rgba.data()), Py_ssize_t(rgba.size() * sizeof(float)));
+    return Py_BuildValue("iiN", W, H, bytes); // N: the tuple takes over the reference
 }
 
 PyMethodDef g_methods[] = {

@@ -184,6 +184,7 @@ typedef struct crt_render_stats {
     uint64_t shadow_rays;     /* only in shadows mode                                                 */
     uint64_t node_tests;      /* boxes tested / k-d nodes visited                                     */
     uint64_t tri_tests;
+    uint64_t entered_rays;    /* rays that enter the root box, i.e. that a walk is started for (<= rays)   */
 } crt_render_stats;
 
 void crt_render_params_default(crt_render_params *p);

@@ -93,7 +93,8 @@ extern "C" {
 // closest hit of every ray through LeanWalker; rays = n x {origin xyz, direction xyz}.  visits_out (optional): nodes
 // loaded per ray.  `lazy_best`: how many leaf visits pass before the pruning threshold sees a new hit (the device tests
 // parked leaves late, so its walk prunes with a stale best distance: 0 = immediately, k = after k more leaves).
-int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int lazy_best, int32_t *tri_out, float *t_out, int32_t *visits_out) {
+int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int lazy_best, int32_t *tri_out, float *t_out, int32_t *visits_out,
+                      long long *rare_events) {
     if (!s || !rays || !s->fast_nodes)
         return -1;
     std::vector<Entry> spill(64);
@@ -109,35 +110,40 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
             w.start(ws, 0u, o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_enter, t_exit);
             float seen_t = best.t; // the distance the pruning uses
             int pending = 0;
+            bool refuse_next = false;
             while (!w.done()) {
                 if (w.sp - w.lo > crtwalk::kWin || w.sp > 60)
                     return -2; // stack discipline broken
-                bool need_pop;
-                if (w.tmin > crtwalk::prune_threshold(seen_t)) {
-                    need_pop = !w.pruned_everything(seen_t);
-                } else {
+                const float threshold = crtwalk::prune_threshold(seen_t);
+                Node node{ 0, 0, 0, 0 };
+                if (!(w.tmin > threshold)) {
                     const crt_kd_node &k = s->fast_nodes[w.node];
                     ++visits;
-                    Node node;
                     std::memcpy(&node.x, &k.split, 4);
                     node.y = k.a, node.z = k.b, node.w = k.axis;
-                    if (node.w == 3) {
-                        for (int i = 0; i < node.z; ++i) {
-                            const uint32_t ref = s->fast_refs[node.y + i];
-                            float t;
-                            if (triangle_test(*s, ref, o, d, t))
-                                best.offer(t, int(ref & 0x7FFFFFFFu));
-                        }
-                        if (++pending > lazy_best)
-                            seen_t = best.t, pending = 0;
-                        need_pop = true;
-                    } else {
-                        w.step(ws, spill.data(), 0u, 0u, node);
-                        need_pop = w.node < 0;
-                    }
                 }
-                if (need_pop)
-                    w.pop(ws, spill.data(), 0u);
+                // every other leaf is refused once (no room) and must be offered again: the device's blocked lanes
+                const bool room = !(refuse_next && node.w == 3);
+                bool took_leaf = false;
+                const bool stopped = w.visit(ws, 0u, 0u, node, threshold, seen_t, room, took_leaf);
+                if (stopped && node.w == 3 && !room && !(w.tmin > threshold))
+                    refuse_next = false; // refused once: the next offer of this leaf is taken
+                if (took_leaf) {
+                    refuse_next = true;
+                    for (int i = 0; i < node.z; ++i) {
+                        const uint32_t ref = s->fast_refs[node.y + i];
+                        float t;
+                        if (triangle_test(*s, ref, o, d, t))
+                            best.offer(t, int(ref & 0x7FFFFFFFu));
+                    }
+                    if (++pending > lazy_best)
+                        seen_t = best.t, pending = 0;
+                }
+                if (stopped) {
+                    const int lo_before = w.lo;
+                    w.make_room(ws, spill.data(), 0u);
+                    *rare_events += w.lo != lo_before;
+                }
                 if (visits > 50000000)
                     return -3; // runaway walk
             }

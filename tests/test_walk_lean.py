@@ -36,7 +36,9 @@ def closest(host, flat, rays, lazy=0, brute=False):
     if brute:
         rc = host.brute_closest(C.byref(flat), p(rays), n, p(tri), p(t))
     else:
-        rc = host.walk_lean_closest(C.byref(flat), p(rays), n, lazy, p(tri), p(t), p(visits))
+        rare = C.c_longlong(0)
+        rc = host.walk_lean_closest(C.byref(flat), p(rays), n, lazy, p(tri), p(t), p(visits), C.byref(rare))
+        closest.rare_events = rare.value
     assert rc == 0, rc
     return tri, t, visits
 
@@ -118,6 +120,18 @@ def test_lean_walk_on_height_fields(crt, ot, host, quads, material):
     want_tri, want_t, _ = closest(host, flat, rays, brute=True)
     tri, t, visits = closest(host, flat, rays, lazy=2)
     assert np.array_equal(tri, want_tri) and np.array_equal(otools.bits(t), otools.bits(want_t))
+
+
+def test_lean_walk_with_a_deep_stack_spills_and_comes_back(crt, ot, host):
+    """11-01/scene8's walk tree is 26 levels deep: the 8-entry stack window overflows for some rays, entries go to the
+    spill array and come back (kWindowFull / kTopSpilled), and the winners are still the brute-force winners"""
+    rel = "11-01-refractive/scene8.crtscene"
+    flat = crt.Scene.load_json(ot.scene_variant(rel, 160, 90), os.path.dirname(ot.scene_file(rel))).flatten(reference_tree=False)
+    rays = ray_set(flat, ot, np.random.default_rng(3), n_primary=8000, n_secondary=8000)
+    want_tri, want_t, _ = closest(host, flat, rays, brute=True)
+    tri, t, _ = closest(host, flat, rays, lazy=1)
+    assert np.array_equal(tri, want_tri) and np.array_equal(otools.bits(t), otools.bits(want_t))
+    assert closest.rare_events > 0, "no ray overflowed the stack window: pick a deeper scene"
 
 
 def test_lean_walk_work_is_bounded(crt, ot, host):
