@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "crt_scene_load_file", "crt_scene_load_json", "crt_scene_flatten", "crt_scene_flatten_ex", "crt_scene_set_camera", "crt_scene_set_resolution",
     "crt_scene_free", "crt_scene_last_error", "crt_render_params_default", "crt_cuda_device_count", "crt_cuda_create",
     "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_pack_walk_tree", "crt_cuda_walk_node_bytes", "crt_cuda_set_camera",
-    "crt_cuda_render", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
+    "crt_cuda_render", "crt_cuda_render_frame", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
     "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
     "crt_cuda_frame_create", "crt_cuda_frame_open", "crt_cuda_frame_attach", "crt_cuda_frame_pointer", "crt_cuda_push_bands",
     "crt_cuda_group_create", "crt_cuda_group_destroy", "crt_cuda_group_last_error", "crt_cuda_group_size", "crt_cuda_group_upload_scene",
@@ -128,6 +128,7 @@ def _load_library():
         "crt_cuda_upload_scene": (C.c_int, [vp, P(FlatScene)]),
         "crt_cuda_set_camera": (C.c_int, [vp, P(Camera)]),
         "crt_cuda_render": (C.c_int, [vp, P(RenderParams), vp, vp, P(RenderStats)]),
+        "crt_cuda_render_frame": (C.c_int, [vp, P(RenderParams), vp, vp, P(RenderStats)]),
         "crt_cuda_render_device": (C.c_int, [vp, P(RenderParams), P(RenderStats)]),
         "crt_cuda_device_framebuffer": (C.c_int, [vp, P(vp), P(vp), P(C.c_int), P(C.c_int)]),
         "crt_cuda_synchronize": (C.c_int, [vp, P(RenderStats)]),
@@ -283,6 +284,14 @@ class Renderer:
         rc = lib.crt_cuda_render(self._ctx, C.byref(params), _ptr(rgb), _ptr(rgb8), C.byref(stats))
         self._check(rc, "crt_cuda_render")
         return rgb, rgb8, stats.as_dict()
+
+    def render_frame(self, params: RenderParams, rgb_frame: int | None = None, rgb8_frame: int | None = None):
+        """crt_cuda_render_frame: this rank's row bands go to their place in a FULL frame in host memory (raw pointers,
+        e.g. of a page-locked shared-memory segment every rank has mapped).  Returns the stats dict."""
+        stats = RenderStats()
+        rc = lib.crt_cuda_render_frame(self._ctx, C.byref(params), C.c_void_p(rgb_frame), C.c_void_p(rgb8_frame), C.byref(stats))
+        self._check(rc, "crt_cuda_render_frame")
+        return stats.as_dict()
 
     def render_device(self, params: RenderParams | None = None):
         params = params or default_params()

@@ -691,6 +691,59 @@ int crt_cuda_render(crt_cuda_ctx *ctx, const crt_render_params *params, float *r
     return CRT_OK;
 }
 
+// this rank's row bands -> their place in a full frame in host memory: one strided copy for the whole bands, one more
+// for a shorter last band of the image when this rank owns it
+static int copy_bands_to_frame(crt_cuda_ctx *ctx, const void *dev_rows, void *frame, size_t pixel_bytes) {
+    const crt_render_params &p = ctx->last_params;
+    const int H = ctx->scene.cam.height, world = p.world > 1 ? p.world : 1, rank = p.world > 1 ? p.rank : 0;
+    const int band = p.band_rows > 0 ? p.band_rows : 8;
+    const size_t row_bytes = size_t(ctx->last_width) * pixel_bytes;
+    if (world == 1) {
+        CRT_CK(ctx, cudaMemcpyAsync(frame, dev_rows, size_t(ctx->last_rows) * row_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        return CRT_OK;
+    }
+    const int bands = (H + band - 1) / band;
+    const int owned = rank < bands ? (bands - 1 - rank) / world + 1 : 0;
+    const int last_rows = H - (bands - 1) * band; // rows of the image's last band
+    const bool short_last = owned > 0 && last_rows < band && (bands - 1) % world == rank;
+    const int whole = owned - (short_last ? 1 : 0);
+    char *dst = static_cast<char *>(frame);
+    const char *src = static_cast<const char *>(dev_rows);
+    if (whole > 0)
+        CRT_CK(ctx, cudaMemcpy2DAsync(dst + size_t(rank) * band * row_bytes, size_t(world) * band * row_bytes, src, size_t(band) * row_bytes,
+                                      size_t(band) * row_bytes, size_t(whole), cudaMemcpyDeviceToHost, ctx->stream));
+    if (short_last)
+        CRT_CK(ctx, cudaMemcpyAsync(dst + size_t(bands - 1) * band * row_bytes, src + size_t(whole) * band * row_bytes, size_t(last_rows) * row_bytes,
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+    return CRT_OK;
+}
+
+int crt_cuda_render_frame(crt_cuda_ctx *ctx, const crt_render_params *params, float *rgb_frame, uint8_t *rgb8_frame, crt_render_stats *stats) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (int rc = enqueue_frame(ctx, params))
+        return rc;
+    for (int pass = 0; pass < 2; ++pass) {
+        if (ctx->last_rows > 0 && ctx->last_width > 0) {
+            if (rgb_frame)
+                if (int rc = copy_bands_to_frame(ctx, ctx->d_rgb, rgb_frame, 3 * sizeof(float)))
+                    return rc;
+            if (rgb8_frame)
+                if (int rc = copy_bands_to_frame(ctx, ctx->d_rgb8, rgb8_frame, 3))
+                    return rc;
+        }
+        if (pass == 0) {
+            if (int rc = crt_cuda_synchronize(ctx, stats))
+                return rc;
+            if (!ctx->rerendered) // (a re-rendered frame -- ray pool grown -- is copied once more)
+                break;
+        } else {
+            CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+    }
+    return CRT_OK;
+}
+
 int crt_cuda_device_framebuffer(crt_cuda_ctx *ctx, void **rgb_dev, void **rgb8_dev, int *width, int *rows) {
     if (!ctx)
         return CRT_ERR_INVALID;

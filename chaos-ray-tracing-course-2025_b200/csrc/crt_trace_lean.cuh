@@ -26,10 +26,13 @@ namespace crtdev {
 #define CRT_N_WAITERS 6
 #endif
 #ifndef CRT_N_MINBLOCKS
-#define CRT_N_MINBLOCKS 10
+#define CRT_N_MINBLOCKS 9 // 56 registers, nothing spilled (r2b: 10 blocks = 48 registers spill ~100 B around the refill and cost 2 %)
 #endif
 #ifndef CRT_N_REFILL
 #define CRT_N_REFILL 25
+#endif
+#ifndef CRT_PREFETCH_PUSH
+#define CRT_PREFETCH_PUSH 0
 #endif
 
 static_assert(crtwalk::kWin == kWin, "stack window of the lean walker and of LightWarpShared");
@@ -98,7 +101,14 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
                 ++cn.node_tests;
         }
         bool took_leaf;
+#if CRT_PREFETCH_PUSH
+        int pushed;
+        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, &pushed);
+        if (pushed >= 0) // the second child will be popped later: have its record on the way (L2) by then
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(&S.kd_nodes[pushed]));
+#else
         stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf);
+#endif
         const bool park = took_leaf & (n.z > 0); // (a leaf without triangles is over at once)
         const bool to0 = park & (parked0 < 0), to1 = park & (parked0 >= 0);
         parked0 = to0 ? at : parked0;
@@ -213,7 +223,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
                     V3 o, d, inv;
                     float t_enter, t_exit;
                     if (level == 0) {
-                        const float4 rd = b.ray0_d[i], ri = b.ray0_i[i];
+                        const float4 rd = get_stream(&b.ray0_d[i]), ri = get_stream(&b.ray0_i[i]);
                         node_id = b.ray0_slot[i];
                         o = mk(S.cam.position[0], S.cam.position[1], S.cam.position[2]);
                         d = xyz(rd), inv = xyz(ri), t_enter = rd.w, t_exit = ri.w;
@@ -277,7 +287,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
                 h.t = __uint_as_float(unsigned(key >> 32));
                 h.tri = int(unsigned(key & 0xffffffffull));
             }
-            b.hit[node_id] = make_float2(h.t, __int_as_float(h.tri));
+            put_stream(&b.hit[node_id], make_float2(h.t, __int_as_float(h.tri)));
             my = -1;
         }
     }

@@ -115,7 +115,8 @@ struct LeanWalker {
     //   With a wide margin and no in-plane entry pending, everything on the stack is beyond it as well (exit distances
     //   grow towards the bottom of the stack, and each interval starts where the one above it ends): the walk is over.
     template <class WS>
-    CRT_WALK_FN bool visit(WS &ws, unsigned lane, unsigned src, const Node n, float threshold, float best_t, bool leaf_room, bool &took_leaf) {
+    CRT_WALK_FN bool visit(WS &ws, unsigned lane, unsigned src, const Node n, float threshold, float best_t, bool leaf_room, bool &took_leaf,
+                           int *pushed = nullptr) {
         const bool pruned = tmin > threshold;
         const bool leaf = n.w == 3;
         const bool inner = !pruned & !leaf;
@@ -146,6 +147,8 @@ struct LeanWalker {
             ws.stack[sp & (kWin - 1)][lane].y = float_to_bits(tmax);
         }
         sp += push ? 1 : 0;
+        if (pushed)
+            *pushed = push ? second : -1; // (for a prefetch of the node the walk will come back to)
         flagged += (push & in_plane) ? 1 : 0;
         tmax = push ? fminf(tmax, tp) : tmax; // NaN: unchanged
         const bool moved = (go_first | go_second) & !frozen;

@@ -54,8 +54,9 @@ typedef struct crt_box_node {
  * axis depth%3 (crt_aabb.h:24-35), the tree is a k-d tree: an inner node is fully described by the cut.
  * inner: {split plane, child0 (or -1), child1 (or -1), axis 0..2};  leaf: {0, first_ref, count, 3}.
  * Two arrays use it: kd_nodes mirrors the reference tree node for node (same indices as box_nodes, leaf lists in
- * refs); fast_nodes is what CRT_TRAVERSAL_KD walks: the same tree after the flattener merged the subtrees whose
- * splits do not pay (cost estimate on the reference's boxes) and stored identical leaf lists once (fast_refs). */
+ * refs); fast_nodes is what CRT_TRAVERSAL_KD walks: OUR OWN surface-area-heuristic k-d tree over the root box
+ * (core/crt_kdbuild.cpp; leaf lists in fast_refs), or -- $CRT_WALK_TREE=reference -- the reference tree after the
+ * flattener merged the subtrees whose splits do not pay and stored identical leaf lists once. */
 typedef struct crt_kd_node {
     float split;
     int32_t a;
@@ -206,8 +207,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *scene);
  * reference, high word = 3 | count << 2.  The root stays node 0.  CRT_ERR_INVALID for a broken tree (shared nodes
  * that do not unfold into n_nodes records, a bad axis, an index out of range, more than 2^28 nodes). */
 int crt_cuda_pack_walk_tree(const crt_kd_node *nodes, int32_t n_nodes, uint64_t *out);
-/* bytes of one walk-tree node as the kernels of this build read it (8; 16 when built with -DCRT_NODE8=0): what the
- * algorithmic bytes per ray of a measurement are counted with */
+/* bytes of one walk-tree node as the kernels of this build read it (16: crt_kd_node as it is; 8 when built with
+ * -DCRT_NODE8=1, the packed record of crt_cuda_pack_walk_tree): what the algorithmic bytes per ray of a measurement are
+ * counted with */
 int crt_cuda_walk_node_bytes(void);
 /* cheap per-frame update (animation): only the 72 B camera block */
 int crt_cuda_set_camera(crt_cuda_ctx *ctx, const crt_camera *camera);
@@ -216,6 +218,12 @@ int crt_cuda_set_camera(crt_cuda_ctx *ctx, const crt_camera *camera);
  * crt_image.h:11-27) or NULL; rgb8_out: width*rows*3 bytes quantised exactly like write_ppm
  * (crt_image_ppm.cpp:16-19) or NULL.  Host pointers; the call returns after the copies complete. */
 int crt_cuda_render(crt_cuda_ctx *ctx, const crt_render_params *params, float *rgb_out, uint8_t *rgb8_out, crt_render_stats *stats);
+/* The same render for ONE FRAME SHARED BY SEVERAL RANKS (params->world > 1): rgb_frame / rgb8_frame point at the FULL
+ * frame in host memory (width*height*3 floats / bytes, row 0 = top) -- e.g. a shared-memory segment that every rank
+ * has mapped and page-locked -- and this rank's row bands are copied to their place in it, over this GPU's own PCIe
+ * link: the frame the reference's bucket threads assemble in `buffer[y*W + x]` (crt_renderer.cpp:171-196), assembled by
+ * N copy engines.  With world <= 1 it is crt_cuda_render. */
+int crt_cuda_render_frame(crt_cuda_ctx *ctx, const crt_render_params *params, float *rgb_frame, uint8_t *rgb8_frame, crt_render_stats *stats);
 /* same, results stay in device memory (see crt_cuda_device_framebuffer); asynchronous on the stream */
 int crt_cuda_render_device(crt_cuda_ctx *ctx, const crt_render_params *params, crt_render_stats *stats);
 /* device pointers of the last frame: float rgb (12 B/px) and u8 rgb (3 B/px); rows = owned rows */
