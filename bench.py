@@ -446,19 +446,20 @@ def run_ours(args):
             gather.gather(D.wrap_device_bytes(rgb8_ptr, w * rows * 3, device))
 
     def timed_steps(n, first_step):
-        """n steps, each bracketed by events on the launch stream, L2 flushed before each; returns per-step ms"""
+        """n steps, each bracketed by events on the launch stream, L2 flushed before each (outside the bracket); the
+        host does NOT wait between steps, so the launches of step s+1 are queued while step s runs: a bracket measures
+        the device, not how fast one host thread can issue a dozen launches into an idle GPU (r2c: the 11 launches of a
+        C5 frame take the host 0.65 ms that way, the device 0.31 ms).  Returns per-step ms."""
         begin = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
         end = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
-        kernel_ms = []
         for s in range(n):
-            flush.fill_(s & 0xFF)  # L2 flush between timed iterations (outside the event bracket)
+            flush.fill_(s & 0xFF)
             begin[s].record(stream)
             device_step(first_step + s)
             end[s].record(stream)
-            if n <= 64:
-                kernel_ms.append(renderer.synchronize()["gpu_ms"])
         torch.cuda.synchronize(device)
-        return [b.elapsed_time(e) for b, e in zip(begin, end)], kernel_ms
+        renderer.synchronize()  # (the context's own bookkeeping: ray-pool flags of the last frame)
+        return [b.elapsed_time(e) for b, e in zip(begin, end)]
 
     for s in range(args.warmup):
         device_step(s)
@@ -467,7 +468,7 @@ def run_ours(args):
         dist.barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     wall0 = time.perf_counter()
-    step_ms, kernel_ms = timed_steps(args.steps, args.warmup)
+    step_ms = timed_steps(args.steps, args.warmup)
     if world > 1:
         dist.barrier()
     wall1 = time.perf_counter()
@@ -479,7 +480,7 @@ def run_ours(args):
     if args.sustain > 0 and world == 1:
         n_sus = max(args.steps, int(args.sustain * 1e3 / max(1e-3, sum(step_ms) / len(step_ms) + 0.15)))
         s0 = time.perf_counter()
-        sus_ms, _ = timed_steps(n_sus, args.warmup)
+        sus_ms = timed_steps(n_sus, args.warmup)
         s1 = time.perf_counter()
         sus_clocks = sampler.window(s0, s1) if sampler else None
         sustain = {"frames": n_sus, "seconds": s1 - s0, "ms_per_step": statistics.mean(sus_ms), "ms_per_step_last_quarter": statistics.mean(sus_ms[-max(1, n_sus // 4):]),
@@ -554,7 +555,8 @@ def run_ours(args):
     rows_local = len(crt.Renderer.owned_rows(H, params.rank, params.world, params.band_rows))
     node_bytes = crt.lib.crt_cuda_walk_node_bytes()  # 16: crt_kd_node as it is (8 with -DCRT_NODE8=1)
     alg_bytes = (node_bytes * counted["node_tests"] + 48 * counted["tri_tests"] + 16 * counted["rays"]) / n_counted + 15.0 * W * rows_local
-    k_ms = statistics.mean(kernel_ms) if kernel_ms else ms_per_step
+    # the render kernels of one frame on this rank: the step's own bracket (at N > 1 it also holds the band push and the barrier)
+    k_ms = statistics.mean(step_ms)
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     prof = {}
     traffic_path = os.path.join(ROOT, "profiles", "traffic.json")  # per frame, from the committed ncu --set full capture of the same kernels
