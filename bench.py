@@ -474,6 +474,12 @@ def run_ours(args):
     wall1 = time.perf_counter()
     total_ms = all_max(sum(step_ms))
     clocks = sampler.window(wall0, wall1) if sampler else None
+    per_rank = [None] * world  # every rank's own view of its steps (the line reports the slowest rank)
+    mine = {"rank": rank, "ms_mean": statistics.mean(step_ms), "ms_min": min(step_ms), "ms_median": statistics.median(step_ms), "ms_max": max(step_ms)}
+    if world > 1:
+        dist.all_gather_object(per_rank, mine)
+    else:
+        per_rank = [mine]
 
     # --- sustained: the same steps back to back for >= args.sustain seconds (does the clock of the 60 ms region hold?)
     sustain = None
@@ -607,7 +613,7 @@ def run_ours(args):
                         "Mrays_per_s_traversing": job_entered_per_step / (ms_per_step * 1e-3) / 1e6,
                         "rays_per_frame_counted_on_this_rank": n_rays, "rays_per_frame_golden": mean_gold,
                         "scene_load_s": t_load, "scene_upload_s": t_upload, "scene_bytes": int(flat.n_triangles * 64 + flat.n_fast_nodes * 16 + flat.n_fast_refs * 4),
-                        "numa": numa, "frames_per_step": world if frames_mode and world > 1 else 1},
+                        "numa": numa, "frames_per_step": world if frames_mode and world > 1 else 1, "per_rank_step_ms": per_rank},
             "clocks": clocks, "sustain": sustain, "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": (72 + 56) * world, "d2h_bytes_per_step": d2h_rgb,
                     "ms_per_step": t_e2e / args.steps * 1e3,

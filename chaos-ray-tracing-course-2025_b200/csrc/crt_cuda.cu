@@ -36,6 +36,9 @@ struct crt_cuda_ctx {
     bool has_secondary = false; // some material can spawn reflection / refraction rays
     int bucket_size = 0;        // Scene::bucket_size: only decides whether the frame gets any bucket at all (enqueue_frame)
     bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
+    const char *warm_base = nullptr; // what a k-d walk reads: triangles .. walk tree .. leaf references, one range of the arena
+    size_t warm_bytes = 0;
+    int warm_mode = -1;              // $CRT_WARM_L2: 0 never, 1 always, -1 by scene size
     int packet_mode = -1;        // primary level as warp packets (crt_trace_packet.cuh): -1 by pixels per triangle, 0 / 1 = $CRT_PACKET
     bool packet_primary = false; // this frame's decision
     crt_render_params last_params{};
@@ -207,11 +210,19 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     ctx->last_width = W;
     ctx->last_rows = dp.rows;
     ctx->last_launches = 0;
+    int extra_launches = 0;
     ctx->last_wavefront = false;
     ctx->last_params = *params;
     if (stats)
         CRT_CK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), ctx->stream));
     CRT_CK(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
+    // the walk's working set on its way into L2 while the first kernels start (k_warm_l2, crt_push.cuh): pays when the
+    // set is large enough to be fetched miss by miss otherwise, and small enough to stay
+    if (params->traversal == CRT_TRAVERSAL_KD && ctx->warm_bytes > 0 &&
+        (ctx->warm_mode == 1 || (ctx->warm_mode < 0 && ctx->warm_bytes >= (size_t(4) << 20) && ctx->warm_bytes <= (size_t(120) << 20)))) {
+        k_warm_l2<<<148 * 4, 256, 0, ctx->stream>>>(ctx->warm_base, ctx->warm_bytes);
+        ++extra_launches;
+    }
     // render_image cuts the frame into int(float(extent) / bucket_size + 0.5) buckets per axis, the last one absorbing
     // the remainder (crt_renderer.cpp:160-170): an image narrower or lower than half a bucket gets NO bucket and
     // stays the zero-initialised Image -- reproduced; otherwise the bucket size has no effect on the pixels
@@ -311,6 +322,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
         }
         CRT_CK(ctx, cudaGetLastError());
     }
+    ctx->last_launches += extra_launches;
     CRT_CK(ctx, cudaEventRecord(ctx->ev_end, ctx->stream));
     if (stats)
         CRT_CK(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, ctx->stream));
@@ -497,12 +509,18 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         { s->texels, size_t(s->n_texels) * sizeof(crt_float4), 0 },
         { s->fast_refs, size_t(s->n_fast_refs) * sizeof(uint32_t), 0 },
     };
-    size_t total = 0;
-    for (Part &p : parts) {
+    // arena order: what a k-d walk reads (triangles, walk tree, its leaf references) first and in one piece -- the range
+    // k_warm_l2 brings into L2 at the start of a frame -- then everything the shading reads, then the reference's tree
+    const int order[12] = { 0, 5, 11, 1, 2, 3, 7, 8, 9, 10, 4, 6 };
+    size_t total = 0, warm_end = 0;
+    for (int k = 0; k < 12; ++k) {
+        Part &p = parts[order[k]];
         if (p.bytes && !p.src)
             return fail(ctx, CRT_ERR_INVALID, "scene array pointer is NULL");
         p.offset = total;
         total += align_up((p.bytes ? p.bytes : 16) + (&p == &parts[5] ? sizeof(KdNodeRec) : 0), 256);
+        if (k == 2)
+            warm_end = total;
     }
     if (total > ctx->d_arena_cap) {
         cudaFree(ctx->d_arena);
@@ -570,6 +588,10 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // r1z_packet_sweep.txt: height fields covering a quarter of the frame): 5-25 % ahead of the per-lane walk from ~60
     // frame pixels per triangle upwards (C1 0.19 -> 0.17 ms, C3 0.82 -> 0.63 ms, C5 0.69 -> 0.63 ms), 1.3-3x BEHIND it
     // below 20 (C4: 8 pixels per triangle).  Threshold 64; $CRT_PACKET=0|1 overrides.
+    ctx->warm_base = ctx->d_arena, ctx->warm_bytes = warm_end;
+    ctx->warm_mode = -1;
+    if (const char *k = std::getenv("CRT_WARM_L2"); k && *k)
+        ctx->warm_mode = *k == '1' ? 1 : 0;
     if (const char *k = std::getenv("CRT_WALKER"); k && *k)
         ctx->wf.classic_walker = std::strcmp(k, "classic") == 0;
     ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)
