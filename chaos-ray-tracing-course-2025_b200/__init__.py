@@ -28,7 +28,7 @@ REF_CULL_BIT = 0x80000000
 EXPORTED_SYMBOLS = [
     "crt_scene_load_file", "crt_scene_load_json", "crt_scene_flatten", "crt_scene_flatten_ex", "crt_scene_set_camera", "crt_scene_set_resolution",
     "crt_scene_free", "crt_scene_last_error", "crt_render_params_default", "crt_cuda_device_count", "crt_cuda_create",
-    "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_pack_walk_tree", "crt_cuda_walk_node_bytes", "crt_cuda_set_camera",
+    "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_pack_walk_tree", "crt_cuda_walk_node_bytes", "crt_cuda_set_camera", "crt_cuda_update_shading", "crt_cuda_group_update_shading",
     "crt_cuda_render", "crt_cuda_render_frame", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
     "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
     "crt_cuda_frame_create", "crt_cuda_frame_open", "crt_cuda_frame_attach", "crt_cuda_frame_pointer", "crt_cuda_push_bands",
@@ -127,6 +127,8 @@ def _load_library():
         "crt_cuda_set_stream": (C.c_int, [vp, vp]),
         "crt_cuda_upload_scene": (C.c_int, [vp, P(FlatScene)]),
         "crt_cuda_set_camera": (C.c_int, [vp, P(Camera)]),
+        "crt_cuda_update_shading": (C.c_int, [vp, P(FlatScene)]),
+        "crt_cuda_group_update_shading": (C.c_int, [vp, P(FlatScene)]),
         "crt_cuda_render": (C.c_int, [vp, P(RenderParams), vp, vp, P(RenderStats)]),
         "crt_cuda_render_frame": (C.c_int, [vp, P(RenderParams), vp, vp, P(RenderStats)]),
         "crt_cuda_render_device": (C.c_int, [vp, P(RenderParams), P(RenderStats)]),
@@ -260,6 +262,10 @@ class Renderer:
         self._check(lib.crt_cuda_upload_scene(self._ctx, C.byref(flat)), "crt_cuda_upload_scene")
         self.width, self.height = flat.camera.width, flat.camera.height
         return flat
+
+    def update_shading(self, flat: FlatScene):
+        """lights / materials / texture records / background / flags of `flat` replace the uploaded ones (same counts)"""
+        self._check(lib.crt_cuda_update_shading(self._ctx, C.byref(flat)), "crt_cuda_update_shading")
 
     def set_camera(self, camera: Camera):
         self._check(lib.crt_cuda_set_camera(self._ctx, C.byref(camera)), "crt_cuda_set_camera")

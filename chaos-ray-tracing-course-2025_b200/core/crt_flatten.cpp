@@ -197,6 +197,48 @@ FastTreeStats build_fast_tree(const AccelerationTree &tree, const std::vector<Tr
     return stats;
 }
 
+// lights, materials, texture records (+ bitmap texels when with_texels) and the scalar block: everything of a Scene that
+// can change between two render_image calls without touching the geometry
+void flatten_shading(const Scene &scene, FlatScene &out, bool with_texels) {
+    out.lights.clear(), out.materials.clear(), out.textures.clear();
+    if (with_texels)
+        out.texels.clear();
+    for (const Light &l : scene.lights)
+        out.lights.push_back({ l.position.x, l.position.y, l.position.z, l.intensity });
+    for (const Material &m : scene.materials)
+        out.materials.push_back({ int32_t(m.type), m.albedo_map_texture_index, m.ior, 0 });
+    size_t texel_cursor = 0;
+    for (const Texture &t : scene.textures) {
+        crt_texture f{};
+        f.type = int32_t(t.type);
+        std::memcpy(f.color0, t.color_a.data, 12);
+        std::memcpy(f.color1, t.color_b.data, 12);
+        f.param = t.scalar;
+        if (t.type == TextureType::Bitmap && t.image) {
+            f.width = t.image->width;
+            f.height = t.image->height;
+            f.texel_offset = int32_t(texel_cursor);
+            texel_cursor += t.image->buffer.size();
+            if (with_texels)
+                for (const Color &c : t.image->buffer)
+                    out.texels.push_back({ c.x, c.y, c.z, 0.0f });
+        }
+        out.textures.push_back(f);
+    }
+    crt_flat_scene &v = out.view;
+    std::memcpy(v.background, scene.background_color.data, 12);
+    v.gi_on = scene.gi_on;
+    v.reflections_on = scene.reflections_on;
+    v.refractions_on = scene.refractions_on;
+    v.bucket_size = scene.bucket_size;
+    v.n_lights = int32_t(out.lights.size());
+    v.n_materials = int32_t(out.materials.size());
+    v.n_textures = int32_t(out.textures.size());
+    v.lights = out.lights.data();
+    v.materials = out.materials.data();
+    v.textures = out.textures.data();
+}
+
 void flatten_scene(const Scene &scene, FlatScene &out, bool with_reference_tree) {
     out = FlatScene{};
     const size_t n_tri = scene.triangles.size(), n_vert = scene.vertices.size();
@@ -226,33 +268,10 @@ void flatten_scene(const Scene &scene, FlatScene &out, bool with_reference_tree)
         out.vert_uv[2 * i + 1] = v.uv.y;
     }
 
-    for (const Light &l : scene.lights)
-        out.lights.push_back({ l.position.x, l.position.y, l.position.z, l.intensity });
-    for (const Material &m : scene.materials)
-        out.materials.push_back({ int32_t(m.type), m.albedo_map_texture_index, m.ior, 0 });
-    for (const Texture &t : scene.textures) {
-        crt_texture f{};
-        f.type = int32_t(t.type);
-        std::memcpy(f.color0, t.color_a.data, 12);
-        std::memcpy(f.color1, t.color_b.data, 12);
-        f.param = t.scalar;
-        if (t.type == TextureType::Bitmap && t.image) {
-            f.width = t.image->width;
-            f.height = t.image->height;
-            f.texel_offset = int32_t(out.texels.size());
-            for (const Color &c : t.image->buffer)
-                out.texels.push_back({ c.x, c.y, c.z, 0.0f });
-        }
-        out.textures.push_back(f);
-    }
+    flatten_shading(scene, out, true);
 
     crt_flat_scene &v = out.view;
     v.camera = flatten_camera(scene.camera);
-    std::memcpy(v.background, scene.background_color.data, 12);
-    v.gi_on = scene.gi_on;
-    v.reflections_on = scene.reflections_on;
-    v.refractions_on = scene.refractions_on;
-    v.bucket_size = scene.bucket_size;
     // root box = min / max over every triangle vertex, starting from the empty box (crt_acceleration_tree.cpp:89-94)
     AABB root = AABB::vacuum();
     for (size_t i = 0; i < 3 * n_tri; ++i) {

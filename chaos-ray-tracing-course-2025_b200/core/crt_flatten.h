@@ -32,6 +32,9 @@ crt_camera flatten_camera(const Camera &camera);
 // scene); $CRT_WALK_TREE=reference needs that tree and forces it.  add_reference_tree fills it in later without
 // touching the other arrays.
 void flatten_scene(const Scene &scene, FlatScene &out, bool with_reference_tree = true);
+// only what shading reads and a caller may change between two render_image calls: lights, materials, texture records,
+// background, the gi / reflections / refractions flags, bucket_size (bitmap texels stay as they are unless with_texels)
+void flatten_shading(const Scene &scene, FlatScene &out, bool with_texels = false);
 void add_reference_tree(const Scene &scene, FlatScene &out);
 
 // Derives the walk tree from the reference tree (crt_flatten.cpp); exposed for tests.

@@ -1,6 +1,12 @@
 // crt::render_image on the GPU: flatten (once) -> upload (once) -> kernels -> read back into Image.
-// Replaces the bucket queue + thread pool of the reference (src/core/crt_renderer.cpp:147-199); bucket_size has
-// no semantic effect (pixels are independent) and is ignored.
+// Replaces the bucket queue + thread pool of the reference (src/core/crt_renderer.cpp:147-199).  bucket_size only
+// decides whether the frame gets any bucket at all (an image smaller than half a bucket stays black, as there).
+//
+// What is cached and what is not: the GEOMETRY (vertices, triangles, both trees, bitmap texels) is flattened and
+// uploaded on the first render and kept in Scene::device; the camera, the lights, materials, texture records,
+// background colour, gi / reflections / refractions flags and bucket_size are re-read from the Scene on EVERY call,
+// like the reference does (it reads the Scene on every call).  After editing vertices / triangles / bitmap images, or
+// changing the NUMBER of lights, materials or textures, drop the cache: scene.device.reset().
 #include "crt_renderer.h"
 
 #include <chrono>
@@ -118,6 +124,13 @@ Image render_image(const Scene &scene, const RendererSettings &settings) {
     params.pipeline = env_int("CRT_PIPELINE", CRT_PIPELINE_AUTO);
     params.shadows = env_int("CRT_SHADOWS", 0);
 
+    // lights, materials, texture records, background, flags: whatever the caller changed since the last call
+    flatten_shading(scene, dev.flat, false);
+    if ((dev.group ? crt_cuda_group_update_shading(dev.group, &dev.flat.view) : crt_cuda_update_shading(dev.ctx, &dev.flat.view)) != CRT_OK) {
+        // a count changed: the cached upload no longer describes this Scene
+        scene.device.reset();
+        return render_image(scene, settings);
+    }
     // the camera may have been moved since the upload (Camera::pan_around & co.): resend the 72 B block
     const crt_camera cam = flatten_camera(scene.camera);
     crt_render_stats stats{};

@@ -36,6 +36,7 @@ struct crt_cuda_ctx {
     bool has_secondary = false; // some material can spawn reflection / refraction rays
     int bucket_size = 0;        // Scene::bucket_size: only decides whether the frame gets any bucket at all (enqueue_frame)
     bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
+    size_t off_lights = 0, off_materials = 0, off_textures = 0; // arena offsets of the small shading arrays (crt_cuda_update_shading)
     const char *warm_base = nullptr; // what a k-d walk reads: triangles .. walk tree .. leaf references, one range of the arena
     size_t warm_bytes = 0;
     int warm_mode = -1;              // $CRT_WARM_L2: 0 never, 1 always, -1 by scene size
@@ -124,6 +125,8 @@ DParams device_params(const crt_render_params &p, int height) {
     d.world = p.world;
     d.band_rows = p.band_rows > 0 ? p.band_rows : 8;
     d.rows = owned_rows(p, height);
+    if (const char *v = std::getenv("CRT_COHERENT"); v && *v == '1')
+        d.coherent = 1;
     return d;
 }
 
@@ -588,6 +591,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // r1z_packet_sweep.txt: height fields covering a quarter of the frame): 5-25 % ahead of the per-lane walk from ~60
     // frame pixels per triangle upwards (C1 0.19 -> 0.17 ms, C3 0.82 -> 0.63 ms, C5 0.69 -> 0.63 ms), 1.3-3x BEHIND it
     // below 20 (C4: 8 pixels per triangle).  Threshold 64; $CRT_PACKET=0|1 overrides.
+    ctx->off_lights = parts[7].offset, ctx->off_materials = parts[8].offset, ctx->off_textures = parts[9].offset;
     ctx->warm_base = ctx->d_arena, ctx->warm_bytes = warm_end;
     ctx->warm_mode = -1;
     if (const char *k = std::getenv("CRT_WARM_L2"); k && *k)
@@ -599,6 +603,45 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         ctx->packet_mode = *k == '1' ? 1 : 0;
     ctx->wf.grow = 1.0; // the ray pool is re-sized per scene (it only grows while one scene is rendered)
     ctx->have_scene = true;
+    return CRT_OK;
+}
+
+int crt_cuda_update_shading(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!s || !ctx->have_scene)
+        return fail(ctx, CRT_ERR_INVALID, "update_shading needs an uploaded scene and a flattened one");
+    DScene &d = ctx->scene;
+    if (s->n_lights != d.n_lights || s->n_materials != d.n_materials || s->n_textures != d.n_textures)
+        return fail(ctx, CRT_ERR_INVALID, "update_shading: the number of lights, materials or textures changed -- upload the scene again");
+    if ((s->n_lights && !s->lights) || (s->n_materials && !s->materials) || (s->n_textures && !s->textures))
+        return fail(ctx, CRT_ERR_INVALID, "scene array pointer is NULL");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    struct Small {
+        const void *src;
+        size_t bytes, offset;
+    } small[3] = { { s->lights, size_t(s->n_lights) * sizeof(crt_float4), ctx->off_lights },
+                   { s->materials, size_t(s->n_materials) * sizeof(crt_material), ctx->off_materials },
+                   { s->textures, size_t(s->n_textures) * sizeof(crt_texture), ctx->off_textures } };
+    bool changed = false;
+    for (const Small &p : small)
+        changed = changed || (p.bytes && std::memcmp(ctx->h_arena + p.offset, p.src, p.bytes) != 0);
+    if (changed) {
+        CRT_CK(ctx, cudaStreamSynchronize(ctx->stream)); // the staging bytes of an earlier copy are about to be overwritten
+        for (const Small &p : small)
+            if (p.bytes) {
+                std::memcpy(ctx->h_arena + p.offset, p.src, p.bytes);
+                CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena + p.offset, ctx->h_arena + p.offset, p.bytes, cudaMemcpyHostToDevice, ctx->stream));
+            }
+    }
+    // the scalar block travels with every launch (DScene is a kernel parameter)
+    std::memcpy(d.bg, s->background, sizeof d.bg);
+    d.gi_on = s->gi_on, d.reflections_on = s->reflections_on, d.refractions_on = s->refractions_on;
+    ctx->bucket_size = s->bucket_size;
+    ctx->has_secondary = false;
+    for (int i = 0; i < s->n_materials; ++i)
+        if ((s->materials[i].type == 1 && s->reflections_on) || (s->materials[i].type == 2 && s->refractions_on))
+            ctx->has_secondary = true;
     return CRT_OK;
 }
 
@@ -993,6 +1036,17 @@ int crt_cuda_group_upload_scene(crt_cuda_group *g, const crt_flat_scene *scene) 
         return CRT_ERR_INVALID;
     for (crt_cuda_ctx *ctx : g->ranks)
         if (int rc = crt_cuda_upload_scene(ctx, scene)) {
+            g->error = ctx->error;
+            return rc;
+        }
+    return CRT_OK;
+}
+
+int crt_cuda_group_update_shading(crt_cuda_group *g, const crt_flat_scene *scene) {
+    if (!g)
+        return CRT_ERR_INVALID;
+    for (crt_cuda_ctx *ctx : g->ranks)
+        if (int rc = crt_cuda_update_shading(ctx, scene)) {
             g->error = ctx->error;
             return rc;
         }

@@ -75,6 +75,7 @@ struct DParams {
     int shadows;
     int rank, world, band_rows; // row-band ownership
     int rows;                   // rows this launch renders (owned rows)
+    int coherent;               // measurement aid ($CRT_COHERENT=1, tools/inst_alg.py): the 32 pixels of a patch all take lane 0's ray
 };
 
 struct Counters {

@@ -119,7 +119,11 @@ __global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constan
     for (int first = blockIdx.x * kRaygenBlock + (threadIdx.x & ~31); first < b.P; first += gridDim.x * kRaygenBlock) {
         const int slot = first + int(lane);
         int x, ly;
-        const bool have = slot_pixel(b, S, P, slot, x, ly);
+        bool have = slot_pixel(b, S, P, slot, x, ly);
+        if (P.coherent) { // a fully coherent ray batch: what the non-divergent instruction count per visit is measured on
+            x = __shfl_sync(0xffffffffu, x, 0), ly = __shfl_sync(0xffffffffu, ly, 0);
+            have = __shfl_sync(0xffffffffu, int(have), 0) != 0;
+        }
         Ray r{};
         RaySetup q{};
         q.live = false;
@@ -202,6 +206,11 @@ __global__ void __launch_bounds__(kShadeBlock) k_wf_shade(const __grid_constant_
             if (queued0)
                 i = b.ray0_slot[i];
             have = slot_pixel(b, S, P, i, x, ly);
+            if (P.coherent) { // the ray this slot was traced with (k_wf_raygen): lane 0 of its patch
+                int x0, ly0;
+                have = slot_pixel(b, S, P, i & ~31, x0, ly0);
+                x = x0, ly = ly0;
+            }
         }
         const int node_id = level == 0 ? i : b.P + start + i;
         int kind = kTerminal, children = 0;

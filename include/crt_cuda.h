@@ -211,6 +211,12 @@ int crt_cuda_pack_walk_tree(const crt_kd_node *nodes, int32_t n_nodes, uint64_t 
  * -DCRT_NODE8=1, the packed record of crt_cuda_pack_walk_tree): what the algorithmic bytes per ray of a measurement are
  * counted with */
 int crt_cuda_walk_node_bytes(void);
+/* What shading reads and a caller may change between two frames WITHOUT touching the geometry: lights, materials,
+ * texture records (same counts as uploaded; bitmap texels stay), background, the gi / reflections / refractions flags,
+ * bucket_size.  crt::render_image calls it on every render, because the reference's render_image reads the Scene on
+ * every call (crt_renderer.cpp:157-199).  Nothing is copied when nothing changed.  CRT_ERR_INVALID when a count
+ * changed: upload the scene again. */
+int crt_cuda_update_shading(crt_cuda_ctx *ctx, const crt_flat_scene *scene);
 /* cheap per-frame update (animation): only the 72 B camera block */
 int crt_cuda_set_camera(crt_cuda_ctx *ctx, const crt_camera *camera);
 
@@ -264,6 +270,7 @@ const char *crt_cuda_group_last_error(const crt_cuda_group *group);
 int crt_cuda_group_size(const crt_cuda_group *group);
 int crt_cuda_group_upload_scene(crt_cuda_group *group, const crt_flat_scene *scene);
 int crt_cuda_group_set_camera(crt_cuda_group *group, const crt_camera *camera);
+int crt_cuda_group_update_shading(crt_cuda_group *group, const crt_flat_scene *scene);
 int crt_cuda_group_render(crt_cuda_group *group, const crt_render_params *params, float *rgb_out, uint8_t *rgb8_out, crt_render_stats *stats);
 /* the assembled quantised frame on devices[0] (for crt_cuda_encode_ppm_device) */
 int crt_cuda_group_frame(crt_cuda_group *group, void **frame_dev, int *width, int *height);

@@ -72,3 +72,40 @@ def test_glass_that_needs_a_hundred_rays_per_pixel_is_rendered_not_dropped(crt, 
         assert st3["rays"] == W * H
     finally:
         r.close()
+
+
+def test_update_shading_equals_a_fresh_upload(crt, ot, renderer):
+    """lights / materials / background / flags changed between two renders must reach the device (the
+    reference's render_image reads the Scene on every call); crt_cuda_update_shading re-sends just those"""
+    import json
+    import os
+    rel = "15-01-conclusion/scene1.crtscene"
+    root = os.path.dirname(ot.scene_file(rel))
+    doc = json.loads(ot.scene_variant(rel, 160, 90))
+    base = crt.Scene.load_json(json.dumps(doc), root)
+    renderer.upload(base.flatten(reference_tree=False))
+    before, _, _ = renderer.render(crt.default_params())
+    doc["settings"]["background_color"] = [0.9, 0.1, 0.3]
+    doc["settings"]["reflections_on"] = False
+    doc["lights"][0]["intensity"] = 2.5 * doc["lights"][0]["intensity"]
+    doc["lights"][0]["position"] = [1.0, 6.0, -2.0]
+    for m in doc["materials"]:
+        if isinstance(m.get("albedo"), list):
+            m["albedo"] = [0.3, 0.9, 0.2]
+    edited = crt.Scene.load_json(json.dumps(doc), root)
+    flat_edited = edited.flatten(reference_tree=False)
+    renderer.update_shading(flat_edited)
+    updated, _, st = renderer.render(crt.default_params(collect_stats=1))
+    assert not np.array_equal(otools.bits(updated), otools.bits(before))
+    fresh = crt.Renderer(0)
+    try:
+        fresh.upload(flat_edited)
+        want, _, st_want = fresh.render(crt.default_params(collect_stats=1))
+    finally:
+        fresh.close()
+    assert np.array_equal(otools.bits(updated), otools.bits(want)) and st["rays"] == st_want["rays"]
+    # a changed count is refused, not silently mis-rendered
+    doc["lights"].append({"intensity": 10, "position": [0, 1, 0]})
+    more = crt.Scene.load_json(json.dumps(doc), root).flatten(reference_tree=False)
+    with pytest.raises(crt.CrtError):
+        renderer.update_shading(more)

@@ -17,6 +17,7 @@ traversal = sys.argv[4] if len(sys.argv) > 4 else "kd"
 stats = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 crt = entry.load_package()
 desc, W, H, depth, _ = bench.WORKLOADS[workload]
+depth = int(os.environ.get("CRT_DEPTH", depth))
 size = tuple(int(v) for v in sys.argv[6].split("x")) if len(sys.argv) > 6 else None  # e.g. 540x540: a smaller frame for ncu
 text, root = bench.scene_text(workload, size)
 scene = crt.Scene.load_json(text, root)
