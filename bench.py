@@ -461,12 +461,13 @@ def run_ours(args):
         renderer.synchronize()  # (the context's own bookkeeping: ray-pool flags of the last frame)
         return [b.elapsed_time(e) for b, e in zip(begin, end)]
 
+    sampler = ClockSampler(local) if rank == 0 else None  # (before the barrier: NVML start-up on rank 0 must not delay its first timed step)
     for s in range(args.warmup):
         device_step(s)
     torch.cuda.synchronize(device)
     if world > 1:
         dist.barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
+        torch.cuda.synchronize(device)
     wall0 = time.perf_counter()
     step_ms = timed_steps(args.steps, args.warmup)
     if world > 1:
