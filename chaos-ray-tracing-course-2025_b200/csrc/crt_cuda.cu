@@ -18,7 +18,6 @@
 #include "crt_ppm.cuh"
 #include "crt_push.cuh"
 #include "crt_gi.h"
-#include "crt_quad_build.h"
 
 using namespace crtdev;
 
@@ -499,16 +498,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         size_t bytes;
         size_t offset;
     };
-    // the walk tree two levels per node (crt_walk_quad.h): what k_wf_trace_lean and k_render_persistent walk
-    std::vector<crtquad::Quad> quads;
-    std::vector<crtquad::LeafRec> quad_leaves;
-    int max_pending = 0;
-    if (const char *why = crtquad::build_quads(s->fast_nodes, s->n_fast_nodes, quads, quad_leaves, &max_pending))
-        return fail(ctx, CRT_ERR_INVALID, why);
-    if (max_pending > kQuadSpill)
-        return fail(ctx, CRT_ERR_INVALID, "acceleration tree deeper than the traversal stack (quad walk)");
-    static_assert(sizeof(crtquad::Quad) == 32 && sizeof(crtquad::LeafRec) == 8, "device records of the quad walk");
-    Part parts[14] = {
+    Part parts[12] = {
         { s->tri_verts, size_t(s->n_triangles) * 3 * sizeof(crt_float4), 0 },
         { s->tri_meta, size_t(s->n_triangles) * 4 * sizeof(int32_t), 0 },
         { s->vert_normal, size_t(s->n_vertices) * sizeof(crt_float4), 0 },
@@ -521,20 +511,18 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
         { s->textures, size_t(s->n_textures) * sizeof(crt_texture), 0 },
         { s->texels, size_t(s->n_texels) * sizeof(crt_float4), 0 },
         { s->fast_refs, size_t(s->n_fast_refs) * sizeof(uint32_t), 0 },
-        { quads.data(), quads.size() * sizeof(crtquad::Quad), 0 },
-        { quad_leaves.data(), quad_leaves.size() * sizeof(crtquad::LeafRec), 0 },
     };
     // arena order: what a k-d walk reads (triangles, walk tree, its leaf references) first and in one piece -- the range
     // k_warm_l2 brings into L2 at the start of a frame -- then everything the shading reads, then the reference's tree
-    const int order[14] = { 0, 12, 13, 11, 5, 1, 2, 3, 7, 8, 9, 10, 4, 6 };
+    const int order[12] = { 0, 5, 11, 1, 2, 3, 7, 8, 9, 10, 4, 6 };
     size_t total = 0, warm_end = 0;
-    for (int k = 0; k < 14; ++k) {
+    for (int k = 0; k < 12; ++k) {
         Part &p = parts[order[k]];
         if (p.bytes && !p.src)
             return fail(ctx, CRT_ERR_INVALID, "scene array pointer is NULL");
         p.offset = total;
         total += align_up((p.bytes ? p.bytes : 16) + (&p == &parts[5] ? sizeof(KdNodeRec) : 0), 256);
-        if (k == 3)
+        if (k == 2)
             warm_end = total;
     }
     if (total > ctx->d_arena_cap) {
@@ -574,9 +562,6 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     std::memcpy(d.root_max, s->root_max, sizeof d.root_max);
     d.n_triangles = s->n_triangles, d.n_nodes = s->n_nodes, d.n_lights = s->n_lights, d.n_materials = s->n_materials, d.n_textures = s->n_textures;
     d.kd_empty_leaf = s->n_fast_nodes;
-    d.quad_nodes = reinterpret_cast<const int4 *>(ctx->d_arena + parts[12].offset);
-    d.quad_leaves = reinterpret_cast<const int2 *>(ctx->d_arena + parts[13].offset);
-    d.quad_empty_leaf = int(quad_leaves.size()) - 1;
     d.tri_verts = reinterpret_cast<const float4 *>(ctx->d_arena + parts[0].offset);
     d.tri_meta = reinterpret_cast<const int4 *>(ctx->d_arena + parts[1].offset);
     d.vert_normal = reinterpret_cast<const float4 *>(ctx->d_arena + parts[2].offset);

@@ -41,8 +41,7 @@ struct DScene {
     int gi_on, reflections_on, refractions_on;
     float root_min[3], root_max[3];
     int n_triangles, n_nodes, n_lights, n_materials, n_textures;
-    int kd_empty_leaf; // index of a leaf without triangles that the upload appends to the walk tree
-    int quad_empty_leaf; // id of the empty record at the end of quad_leaves (tombstone of stolen subtrees, crt_trace_lean.cuh)
+    int kd_empty_leaf; // index of a leaf without triangles that the upload appends to the walk tree (tombstone of stolen subtrees)
     const float4 *__restrict__ tri_verts;   // 3 per triangle
     const int4 *__restrict__ tri_meta;      // 1 per triangle
     const float4 *__restrict__ vert_normal; // 1 per vertex
@@ -50,8 +49,6 @@ struct DScene {
     const float4 *__restrict__ box_nodes;   // 2 per node
     const KdNodeRec *__restrict__ kd_nodes; // 1 per node of the walk tree (crt_flat_scene.fast_nodes), see kd_node_at
     const uint32_t *__restrict__ kd_refs;   // its leaf lists (crt_flat_scene.fast_refs)
-    const int4 *__restrict__ quad_nodes;    // the same tree two levels per node (crt_walk_quad.h), 2 x int4 per quad node
-    const int2 *__restrict__ quad_leaves;   // {first reference in kd_refs, count} per leaf
     const uint32_t *__restrict__ refs;      // leaf lists of the reference tree (box_nodes)
     const float4 *__restrict__ lights;
     const int4 *__restrict__ materials;

@@ -95,9 +95,10 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     const float gi_div = float(P.gi_rays + 1u);
     auto no_shadow = [](V3, float) { return false; };
 
-    crtquad::QuadWalker w;
-    uint2 spill[kQuadSpill]; // stack entries below the shared-memory window
-    w.node = crtquad::kDone, w.sp = 1, w.lo = 0, w.flagged = 0, w.tmin = 0.0f, w.tmax = 0.0f;
+    crtwalk::LeanWalker w;
+    uint2 spill[kStack]; // stack entries below the shared-memory window
+    w.node = crtwalk::kDone, w.sp = 1, w.lo = 0, w.flagged = 0, w.tmin = 0.0f, w.tmax = 0.0f;
+    const uint32_t empty_leaf = uint32_t(S.kd_empty_leaf);
     // ---- pixel state
     int px = 0, ply = -1; // my pixel (local row), ply < 0 = no pixel
     int depth = 0;
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
                     fresh = true, live = false;
                     src = lane, stolen = 1;
                     ws.helpers[lane] = 0;
-                    w.node = crtquad::kDone;
+                    w.node = crtwalk::kDone;
                     parked0 = -1, parked1 = -1;
                 }
             }
@@ -149,7 +150,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         // ---- the queue is empty and some lanes have nothing to do: they take over pending subtrees of the lanes that
         //      are still walking (crt_trace_lean.cuh: lean_steal)
         if (exhausted)
-            lean_steal<STATS>(S, ws, w, lane, lt_mask, ply >= 0, helper, src, stolen, cn);
+            lean_steal<STATS>(ws, w, lane, lt_mask, ply >= 0, helper, src, stolen, empty_leaf, cn);
         // ---- walk: a few node visits per lane; a leaf is parked and the walk goes on (crt_trace_lean.cuh: lean_walk)
         bool blocked = false;
         if ((ply >= 0 || helper) && !w.done()) // fresh pixels have a finished walk

@@ -12,12 +12,12 @@
 //   * node visits are counted where the node is loaded (STATS builds).
 #pragma once
 
-#include "crt_walk_quad.h"
+#include "crt_walk_lean.h"
 
 namespace crtdev {
 
 #ifndef CRT_N_STEPS
-#define CRT_N_STEPS 5 // quad-node visits per round (two tree levels each)
+#define CRT_N_STEPS 8
 #endif
 #ifndef CRT_N_TRIGGER
 #define CRT_N_TRIGGER 16
@@ -35,24 +35,24 @@ namespace crtdev {
 #define CRT_PREFETCH_PUSH 0
 #endif
 
-static_assert(crtquad::kWin == kWin, "stack window of the quad walker and of LightWarpShared");
-constexpr int kQuadSpill = 96; // pending entries of a walk: three per quad level and the sentinel; checked at upload
+static_assert(crtwalk::kWin == kWin, "stack window of the lean walker and of LightWarpShared");
+
+__device__ __forceinline__ crtwalk::Node as_walk_node(const int4 n) { return crtwalk::Node{ n.x, n.y, n.z, n.w }; }
 
 // ---- pieces shared with k_render_persistent -----------------------------------------------------------------------
 
 // idle lanes take over the bottom stack entries (the farthest pending subtrees) of lanes that still walk; see
 // k_wf_trace_light for the protocol.  `busy_lane` = this lane owns a ray or helps one; returns through the references.
 template <bool STATS>
-__device__ __forceinline__ void lean_steal(const DScene &S, LightWarpShared &ws, crtquad::QuadWalker &w, unsigned lane, unsigned lt_mask, bool owns_work,
-                                           bool &helper, unsigned &src, int &stolen, Counters &cn) {
+__device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWalker &w, unsigned lane, unsigned lt_mask, bool owns_work, bool &helper,
+                                           unsigned &src, int &stolen, uint32_t empty_leaf, Counters &cn) {
     const unsigned full = 0xffffffffu;
     const bool thief = !owns_work && !helper;
     const unsigned thieves = __ballot_sync(full, thief);
     stolen = max(1, min(stolen, w.sp)); // entries in [1, stolen) are tombstones; popping past them frees the slots
-    const uint2 lowest = ws.stack[stolen & (kWin - 1)][lane];
-    // what can be given away: the lowest live entry when it is a quad node (not a leaf, not a tombstone) that was not
-    // pushed for an in-plane ray (its owner counts those), and something is left for the owner
-    const bool can_give = (owns_work || helper) && !w.done() && w.lo == 0 && w.sp - stolen >= 2 && int(lowest.x) >= 0 && (lowest.y & 0x8000u) == 0u;
+    const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
+    const bool can_give = (owns_work || helper) && !w.done() && w.node >= 0 && w.lo == 0 && w.sp - stolen >= 2 && (lowest & crtwalk::kFlagBit) == 0u &&
+                          lowest != empty_leaf;
     const unsigned victims = __ballot_sync(full, can_give);
     if (thieves != 0u && victims != 0u) {
         const int pairs = min(__popc(thieves), __popc(victims));
@@ -62,54 +62,62 @@ __device__ __forceinline__ void lean_steal(const DScene &S, LightWarpShared &ws,
         const unsigned v_src = __shfl_sync(full, src, v);
         const int v_stolen = __shfl_sync(full, stolen, v);
         if (paired && thief) {
-            const uint2 e = ws.stack[v_stolen & (kWin - 1)][v]; // {quad node, its interval}
+            // the victim's lowest live entry {node, exit}; its interval starts where the entry above it ends
+            const uint2 e = ws.stack[v_stolen & (kWin - 1)][v];
+            const float enter_t = __uint_as_float(ws.stack[(v_stolen + 1) & (kWin - 1)][v].y);
             helper = true;
             src = v_src;
             stolen = 1;
-            w.begin(ws, lane, int(e.x), crtquad::interval_start(e.y), crtquad::interval_exit(e.y));
+            w.begin(ws, lane, int(e.x), enter_t, __uint_as_float(e.y));
             atomicAdd(&ws.helpers[v_src], 1);
         }
         __syncwarp();
         if (paired && !thief) {
-            ws.stack[stolen & (kWin - 1)][lane].x = uint32_t(crtquad::leaf_ref(S.quad_empty_leaf));
+            ws.stack[stolen & (kWin - 1)][lane].x = empty_leaf;
             ++stolen;
         }
         __syncwarp();
     }
 }
 
-// up to STEPS quad-node visits of this lane's walk; a reached leaf is PARKED (its id kept in one of two registers) and
+// up to STEPS node visits of this lane's walk; a reached leaf is PARKED (its node id kept in one of two registers) and
 // the walk goes on -- speculatively: its triangles have not been tested yet, so the distance used for pruning may be
 // stale, never wrong.  Returns true when the lane is blocked on a leaf with both slots taken.
 template <bool STATS, int STEPS>
-__device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, crtquad::QuadWalker &w, uint2 *spill, unsigned lane, unsigned src,
+__device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, crtwalk::LeanWalker &w, uint2 *spill, unsigned lane, unsigned src,
                                           int &parked0, int &parked1, Counters &cn) {
     const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
-    const float threshold = crtquad::prune_threshold(best_t);
+    const float threshold = crtwalk::prune_threshold(best_t);
     bool stopped = false;
 #pragma unroll
     for (int k = 0; k < STEPS; ++k) {
         if (w.done() | stopped)
             break;
-        crtquad::Quad q{};
-        if (w.node >= 0 && !(w.tmin > threshold)) { // (predicated loads: a pruned subtree's node is never fetched)
-            const int4 planes = __ldg(&S.quad_nodes[2 * w.node]), kids = __ldg(&S.quad_nodes[2 * w.node + 1]);
-            q.split_r = planes.x, q.split_a = planes.y, q.split_b = planes.z, q.meta = planes.w;
-            q.c[0] = kids.x, q.c[1] = kids.y, q.c[2] = kids.z, q.c[3] = kids.w;
+        const int at = w.node;
+        int4 n = make_int4(0, 0, 0, 0);
+        if (!(w.tmin > threshold)) { // (a predicated load: a pruned subtree's node is never fetched)
+            n = kd_node_at(S, at);
             if (STATS)
                 ++cn.node_tests;
         }
-        int leaf;
-        stopped = w.visit(ws, lane, src, q, threshold, best_t, parked1 < 0, leaf);
-        const bool park = (leaf >= 0) & (leaf != S.quad_empty_leaf); // (a stolen subtree's tombstone holds nothing)
+        bool took_leaf;
+#if CRT_PREFETCH_PUSH
+        int pushed;
+        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, &pushed);
+        if (pushed >= 0) // the second child will be popped later: have its record on the way (L2) by then
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(&S.kd_nodes[pushed]));
+#else
+        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf);
+#endif
+        const bool park = took_leaf & (n.z > 0); // (a leaf without triangles is over at once)
         const bool to0 = park & (parked0 < 0), to1 = park & (parked0 >= 0);
-        parked0 = to0 ? leaf : parked0;
-        parked1 = to1 ? leaf : parked1;
+        parked0 = to0 ? at : parked0;
+        parked1 = to1 ? at : parked1;
     }
     if (!stopped)
         return false;
-    w.make_room(ws, spill, lane); // (rare: pushes do not fit the stack window / popped entry spilled; nothing to do for a blocked leaf)
-    return !w.done() && w.node <= -2 && parked1 >= 0; // blocked: at a leaf with both slots taken -- the test phase must run first
+    w.make_room(ws, spill, lane); // (rare: stack window full / popped entry spilled; nothing to do for a blocked leaf)
+    return !w.done() && parked1 >= 0; // blocked: both slots taken -- the test phase must run before this lane walks on
 }
 
 // test phase: every parked leaf of every lane at once.  shfl prefix sum of the parked counts, owner lane by binary
@@ -118,15 +126,15 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
 template <bool STATS>
 __device__ __forceinline__ void lean_test_parked(const DScene &S, LightWarpShared &ws, unsigned lane, unsigned src, int parked0, int parked1, Counters &cn) {
     const unsigned full = 0xffffffffu;
-    // the parked leaves' records: {first reference, count}
+    // the parked leaves' records again (they were loaded a few visits ago: L1)
     int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0;
     if (parked0 >= 0) {
-        const int2 n = __ldg(&S.quad_leaves[parked0]);
-        p0_first = n.x, p0_count = n.y;
+        const int4 n = kd_node_at(S, parked0);
+        p0_first = n.y, p0_count = n.z;
     }
     if (parked1 >= 0) {
-        const int2 n = __ldg(&S.quad_leaves[parked1]);
-        p1_first = n.x, p1_count = n.y;
+        const int4 n = kd_node_at(S, parked1);
+        p1_first = n.y, p1_count = n.z;
     }
     const int mine = p0_count + p1_count;
     int incl = mine;
@@ -186,9 +194,10 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     const unsigned full = 0xffffffffu;
-    crtquad::QuadWalker w;
-    uint2 spill[kQuadSpill]; // stack entries below the shared-memory window
-    w.node = crtquad::kDone, w.sp = 1, w.lo = 0, w.flagged = 0, w.tmin = 0.0f, w.tmax = 0.0f;
+    const uint32_t empty_leaf = uint32_t(S.kd_empty_leaf);
+    crtwalk::LeanWalker w;
+    uint2 spill[kStack]; // stack entries below the shared-memory window
+    w.node = crtwalk::kDone, w.sp = 1, w.lo = 0, w.flagged = 0, w.tmin = 0.0f, w.tmax = 0.0f;
     int my = -1;      // index of my ray within the level, -1 = idle
     int node_id = 0;  // where my ray's hit record goes
     bool live = false;
@@ -235,7 +244,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
                     live = t_enter <= t_exit;
                     if (STATS && level > 0 && live)
                         ++cn.entered; // (level 0: counted by the ray generation)
-                    w.node = crtquad::kDone;
+                    w.node = crtwalk::kDone;
                     if (live) {
                         w.start(ws, lane, o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_enter, t_exit);
                         ws.best[lane] = kNoHitKey;
@@ -250,7 +259,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
             continue;
         }
         if (exhausted)
-            lean_steal<STATS>(S, ws, w, lane, lt_mask, my >= 0, helper, src, stolen, cn);
+            lean_steal<STATS>(ws, w, lane, lt_mask, my >= 0, helper, src, stolen, empty_leaf, cn);
         // ---- walk
         bool blocked = false;
         if ((my >= 0 || helper) && !w.done())

@@ -12,7 +12,6 @@
 
 #include "../../include/crt_cuda.h"
 #include "../../chaos-ray-tracing-course-2025_b200/csrc/crt_walk_lean.h"
-#include "../../chaos-ray-tracing-course-2025_b200/csrc/crt_quad_build.h"
 
 namespace {
 
@@ -133,75 +132,6 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
                     refuse_next = true;
                     for (int i = 0; i < node.z; ++i) {
                         const uint32_t ref = s->fast_refs[node.y + i];
-                        float t;
-                        if (triangle_test(*s, ref, o, d, t))
-                            best.offer(t, int(ref & 0x7FFFFFFFu));
-                    }
-                    if (++pending > lazy_best)
-                        seen_t = best.t, pending = 0;
-                }
-                if (stopped) {
-                    const int lo_before = w.lo;
-                    w.make_room(ws, spill.data(), 0u);
-                    *rare_events += w.lo != lo_before;
-                }
-                if (visits > 50000000)
-                    return -3; // runaway walk
-            }
-        }
-        tri_out[r] = best.tri;
-        t_out[r] = best.tri >= 0 ? best.t : 0.0f;
-        if (visits_out)
-            visits_out[r] = visits;
-    }
-    return 0;
-}
-
-// the same through the QUAD walker (crt_walk_quad.h) over the quad nodes crt_quad_build.h folds the binary tree into
-int walk_quad_closest(const crt_flat_scene *s, const float *rays, int n, int lazy_best, int32_t *tri_out, float *t_out, int32_t *visits_out,
-                      long long *rare_events) {
-    if (!s || !rays || !s->fast_nodes)
-        return -1;
-    std::vector<crtquad::Quad> quads;
-    std::vector<crtquad::LeafRec> leaves;
-    int max_pending = 0;
-    if (crtquad::build_quads(s->fast_nodes, s->n_fast_nodes, quads, leaves, &max_pending))
-        return -4;
-    std::vector<Entry> spill(size_t(max_pending) + 8);
-    for (int r = 0; r < n; ++r) {
-        const V o{ rays[6 * r], rays[6 * r + 1], rays[6 * r + 2] }, d{ rays[6 * r + 3], rays[6 * r + 4], rays[6 * r + 5] };
-        V inv;
-        float t_enter, t_exit;
-        Best best;
-        int visits = 0;
-        if (root_interval(*s, o, d, inv, t_enter, t_exit)) {
-            HostWarp ws{};
-            crtquad::QuadWalker w;
-            w.start(ws, 0u, o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_enter, t_exit);
-            float seen_t = best.t;
-            int pending = 0;
-            bool refuse_next = false;
-            while (!w.done()) {
-                if (w.sp - w.lo > crtquad::kWin || w.sp > max_pending || w.sp < 0)
-                    return -2; // stack discipline broken
-                const float threshold = crtquad::prune_threshold(seen_t);
-                crtquad::Quad q{};
-                if (w.node >= 0 && !(w.tmin > threshold)) {
-                    q = quads[size_t(w.node)];
-                    ++visits;
-                }
-                // every other leaf is refused once (no room) and must be offered again: the device's blocked lanes
-                const bool at_leaf = w.node <= -2;
-                const bool room = !(refuse_next && at_leaf);
-                int leaf = -1;
-                const bool stopped = w.visit(ws, 0u, 0u, q, threshold, seen_t, room, leaf);
-                if (stopped && at_leaf && !room)
-                    refuse_next = false;
-                if (leaf >= 0) {
-                    refuse_next = true;
-                    const crtquad::LeafRec &L = leaves[size_t(leaf)];
-                    for (int i = 0; i < L.count; ++i) {
-                        const uint32_t ref = s->fast_refs[L.first + i];
                         float t;
                         if (triangle_test(*s, ref, o, d, t))
                             best.offer(t, int(ref & 0x7FFFFFFFu));

@@ -16,22 +16,19 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 SRC = os.path.join(HERE, "host", "walk_lean_host.cpp")
 LIB = os.path.join(HERE, "host", "_build", "libwalk_lean_host.so")
-HEADERS = [os.path.join(ROOT, "chaos-ray-tracing-course-2025_b200", "csrc", h) for h in ("crt_walk_lean.h", "crt_walk_quad.h", "crt_quad_build.h")]
+HEADER = os.path.join(ROOT, "chaos-ray-tracing-course-2025_b200", "csrc", "crt_walk_lean.h")
 
 
 @pytest.fixture(scope="module")
 def host():
-    if not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(f) for f in [SRC] + HEADERS):
+    if not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(SRC), os.path.getmtime(HEADER)):
         os.makedirs(os.path.dirname(LIB), exist_ok=True)
         subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math", "-I" + os.path.join(ROOT, "include"), SRC, "-o", LIB],
                        check=True)
     return C.CDLL(LIB)
 
 
-WALKER = "walk_quad_closest"  # the walker the device kernels use; "walk_lean_closest" = the binary one (kept for A/B builds)
-
-
-def closest(host, flat, rays, lazy=0, brute=False, walker=None):
+def closest(host, flat, rays, lazy=0, brute=False):
     rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
     n = len(rays)
     tri, t, visits = np.empty(n, np.int32), np.empty(n, np.float32), np.empty(n, np.int32)
@@ -40,7 +37,7 @@ def closest(host, flat, rays, lazy=0, brute=False, walker=None):
         rc = host.brute_closest(C.byref(flat), p(rays), n, p(tri), p(t))
     else:
         rare = C.c_longlong(0)
-        rc = getattr(host, walker or WALKER)(C.byref(flat), p(rays), n, lazy, p(tri), p(t), p(visits), C.byref(rare))
+        rc = host.walk_lean_closest(C.byref(flat), p(rays), n, lazy, p(tri), p(t), p(visits), C.byref(rare))
         closest.rare_events = rare.value
     assert rc == 0, rc
     return tri, t, visits
