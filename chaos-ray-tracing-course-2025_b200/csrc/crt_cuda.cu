@@ -711,8 +711,11 @@ int crt_cuda_render(crt_cuda_ctx *ctx, const crt_render_params *params, float *r
     // resolve.  Off by default: on B200 the overlapped copy (1.8 ms for a 4K float frame) stretches the walk kernels
     // of C4 from 3.05 to 4.2 ms, so the frame reaches the host LATER than with the copy queued behind the kernels
     // (5.03 vs 4.85 ms, tools/e2e_probe.py).
+    // ($CRT_EARLY_COPY=2, measurement aid: the row tracking of mode 1 -- its atomics -- WITHOUT the overlapped copy: what of
+    // the slowdown is the atomics, what is a 100 MB copy streaming through L2 beside kernels that live on their L2 hits)
     const char *early_env = std::getenv("CRT_EARLY_COPY");
-    const bool early_enabled = early_env && *early_env == '1';
+    const bool early_enabled = early_env && (*early_env == '1' || *early_env == '2');
+    const bool overlap_copy = early_env && *early_env == '1';
     ctx->arm_early_copy = rgb_out != nullptr && early_enabled;
     ctx->early_recorded = false;
     if (ctx->wf.h_flags)
@@ -723,7 +726,7 @@ int crt_cuda_render(crt_cuda_ctx *ctx, const crt_render_params *params, float *r
         return enq;
     const size_t pixels = size_t(ctx->last_width) * size_t(ctx->last_rows);
     const size_t row_floats = size_t(ctx->last_width) * 3;
-    const bool early = ctx->early_recorded && pixels;
+    const bool early = ctx->early_recorded && pixels && overlap_copy;
     if (rgb_out && pixels) {
         if (early) {
             CRT_CK(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_primary, 0));

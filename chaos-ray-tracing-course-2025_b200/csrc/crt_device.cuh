@@ -727,7 +727,16 @@ __device__ __forceinline__ void sincos_ref(float a, float &s, float &c) {
 }
 
 // One GI bounce direction, src/core/crt_renderer.cpp:62-74.
+// CRT_GI_OUTLINE = 1: a real function, ONE copy of the two binary64 sine / cosine evaluations, the cross products and the
+// normalisation instead of one per call site (the GI kernel is ~3 400 instructions and its top stall is instruction fetch).
+#ifndef CRT_GI_OUTLINE
+#define CRT_GI_OUTLINE 0
+#endif
+#if CRT_GI_OUTLINE
+__device__ __noinline__ V3 gi_direction(V3 ray_dir, V3 normal, Pcg32 &rng) {
+#else
 __device__ __forceinline__ V3 gi_direction(V3 ray_dir, V3 normal, Pcg32 &rng) {
+#endif
     const float pi = 3.14159274101257324219f;
     const V3 right = normalized(cross(ray_dir, normal));
     const V3 up = normal;

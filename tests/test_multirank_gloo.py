@@ -83,3 +83,50 @@ def test_owned_rows_partition(crt):
                 for r in range(world):
                     assert np.array_equal(rows[r], crt.Renderer.owned_rows(height, r, world, band))
                     assert (np.diff(rows[r]) > 0).all()
+
+
+def _shared_frame_worker(rank, world, port, scene_text, band_rows, out_path):
+    """what bench.py's e2e leg does at N > 1, with the oracle port standing in for the GPU: every rank writes its row
+    bands to their place in ONE frame in shared host memory (bench.SharedHostFrame), nothing is gathered"""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import __graft_entry__ as entry
+    import bench
+    import oracle_tools as ot
+    crt = entry.load_package()
+    from crt_b200 import distributed as D
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        flat = crt.Scene.load_json(scene_text).flatten()
+        W, H = flat.camera.width, flat.camera.height
+        name = [f"crt_test_{os.getpid()}"] if rank == 0 else [None]
+        dist.broadcast_object_list(name, src=0)
+        shared = bench.SharedHostFrame(name[0], W * H * 12, create=True) if rank == 0 else None
+        dist.barrier()
+        if rank != 0:
+            shared = bench.SharedHostFrame(name[0], W * H * 12, create=False)
+        rows = D.owned_rows(H, rank, world, band_rows)
+        shared.touch([(int(r) * W * 12, int(min(H, r + band_rows)) * W * 12) for r in rows[::band_rows]])
+        part = ot.port_render(flat, crt.default_params(rank=rank, world=world, band_rows=band_rows), threads=2, primary=False)
+        frame = shared.array.view(np.float32).reshape(H, W, 3)
+        frame[rows] = part["rgb"]  # (the GPU path: crt_cuda_render_frame, one strided copy per rank)
+        dist.barrier()
+        if rank == 0:
+            np.save(out_path, frame.copy())
+        del frame
+        dist.barrier()
+        shared.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@needs_scenes
+@pytest.mark.parametrize("world,band_rows,size", [(2, 8, (96, 54)), (3, 8, (64, 37))])
+def test_ranks_assemble_one_frame_in_shared_host_memory(crt, ot, tmp_path, world, band_rows, size):
+    text = ot.scene_variant("15-01-conclusion/scene1.crtscene", *size)
+    out = str(tmp_path / "frame.npy")
+    mp.spawn(_shared_frame_worker, args=(world, _free_port(), text, band_rows, out), nprocs=world, join=True)
+    full = ot.port_render(crt.Scene.load_json(text).flatten(), crt.default_params(), primary=False)
+    assert np.array_equal(ot.bits(np.load(out)), ot.bits(full["rgb"]))

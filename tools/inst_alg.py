@@ -24,6 +24,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np  # noqa: E402
 
 os.environ["CRT_COHERENT"] = "1"
+os.environ["CRT_PACKET"] = "0"  # the per-lane walk kernel also where the warp-packet kernel would render the primary level
 import bench  # noqa: E402
 import __graft_entry__ as entry  # noqa: E402
 
@@ -44,7 +45,7 @@ def counted(workload, size):
 def warp_instructions(workload, size):
     cmd = ["ncu", "--metrics", "smsp__inst_executed.sum,smsp__thread_inst_executed.sum", "--clock-control", "none", "-k", "regex:k_wf_trace_lean", "-c", "1", "--csv",
            sys.executable, os.path.join(ROOT, "tools", "render_frames.py"), workload, "1", "wavefront", "kd", "0"] + ([size] if size else [])
-    out = subprocess.run(cmd, env=dict(os.environ, CRT_DEPTH="0"), capture_output=True, text=True, timeout=900).stdout
+    out = subprocess.run(cmd, env=dict(os.environ, CRT_DEPTH="0", CRT_PACKET="0"), capture_output=True, text=True, timeout=900).stdout
     rows = [r for r in csv.reader(io.StringIO(out)) if len(r) > 10 and r[0].isdigit()]
     vals = {r[-3]: float(r[-1].replace(",", "")) for r in rows}
     return vals["smsp__inst_executed.sum"], vals["smsp__thread_inst_executed.sum"]
