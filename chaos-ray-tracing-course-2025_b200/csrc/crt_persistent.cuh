@@ -35,7 +35,7 @@ namespace crtdev {
 #define CRT_P_STEPS_GI 2 // GI queries are short (a diffuse bounce ends at the next surface): more frequent phase changes pay
 #endif
 #ifndef CRT_P_SHADE_TRIGGER_GI
-#define CRT_P_SHADE_TRIGGER_GI 28 // the GI continuation is long (sinf / cosf, basis, PCG): run it for nearly full warps only
+#define CRT_P_SHADE_TRIGGER_GI 20 // the GI continuation is long (sinf / cosf, basis, PCG): run it for well-filled warps only (r2k: 28 -> 164.0 ms, 24 -> 159.9, 20 -> 157.8)
 #endif
 #ifndef CRT_P_SHADE_TRIGGER
 #define CRT_P_SHADE_TRIGGER 12
