@@ -104,11 +104,19 @@ def orbit_of(text: str, frames: int = 240):
     return scenes_module().orbit_cameras([np.float32(v) for v in cam["position"]], [np.float32(v) for v in cam["matrix"]], center, frames)
 
 
+def orbit_frame(k: int, frames: int = 240) -> int:
+    """the k-th frame a job renders.  The orbit is walked in steps of 7 frames (coprime to 240: every frame comes up once
+    in 240) so that a run of 20 steps samples the whole circle whatever N is -- the frames near the scene file's own
+    camera cost twice the orbit's average (r2l: 0.65 ms against 0.31 ms), and a 1-GPU run that only ever saw those would
+    be compared with an 8-GPU run that saw 160 others."""
+    return (7 * k) % frames
+
+
 def partition_text(workload: str, world: int, partition: str, gather: str) -> str:
     if world <= 1:
         return "single GPU"
     if partition == "frames":
-        return ("orbit frame k -> rank k % N: every rank renders a different frame per step, no exchange" if workload == "c5"
+        return ("orbit: the k-th frame of the job (orbit frame 7k mod 240) -> rank k % N, every rank renders a different frame per step, no exchange" if workload == "c5"
                 else "REPLICAS: every rank renders the same whole frame, no exchange (not a scaling measurement of one frame)")
     return f"one frame in interleaved row bands of {BAND_ROWS}, " + ("pushed into rank 0's frame by peer stores over NVLink + 1-element all-reduce as the barrier"
                                                                        if gather == "peer" else "NCCL gather of u8 rgb to rank 0")
@@ -237,7 +245,7 @@ def reference_render(workload: str, frames: int, warmup: int, size=None) -> dict
             orbit = orbit_of(text)
             doc = json.loads(text)
             for k in range(warmup + frames):
-                pos, mat = orbit[k % len(orbit)]
+                pos, mat = orbit[orbit_frame(k, len(orbit))]
                 doc["camera"]["position"] = [float(v) for v in pos]
                 doc["camera"]["matrix"] = [float(v) for v in mat]
                 path = os.path.join(tmp, f"orbit{k}.crtscene")
@@ -247,7 +255,7 @@ def reference_render(workload: str, frames: int, warmup: int, size=None) -> dict
                 os.unlink(path)
                 if k >= warmup:
                     times.append(out["render_s"][1])
-                    rays.append(gold["rays_per_orbit_frame"][k % len(orbit)] if full_size else None)
+                    rays.append(gold["rays_per_orbit_frame"][orbit_frame(k, len(orbit))] if full_size else None)
         else:
             path = os.path.join(tmp, "scene.crtscene")
             open(path, "w").write(text)
@@ -390,7 +398,7 @@ def run_ours(args):
     params = crt.default_params(**common, **part)
 
     def frame_index(step):  # c5: a different orbit frame on every rank, every step
-        return (step * world + rank) % len(orbit)
+        return orbit_frame(step * world + rank, len(orbit))
 
     def camera_for(step):
         cam = crt.Camera.from_buffer_copy(flat.camera)
@@ -577,7 +585,8 @@ def run_ours(args):
             # inst_alg = the kernel's own NON-DIVERGENT warp instructions per node visit / triangle test / ray,
             # measured with ncu on a fully coherent ray batch (profiles/, tools/inst_alg.py); 32 rays share one instruction
             ia = prof["inst_alg"]
-            alg_inst = (ia["per_node_visit"] * counted["node_tests"] + ia["per_triangle_test"] * counted["tri_tests"]
+            walk_visits = counted["node_tests"] - counted["rays"]  # (one "node test" per ray is the root-box test of the ray set-up)
+            alg_inst = (ia["per_node_visit"] * walk_visits + ia["per_triangle_test"] * counted["tri_tests"]
                         + ia.get("per_ray", 0.0) * counted["entered_rays"]) / n_counted / 32.0
             issue.update({"bound": "issue", "algorithmic_warp_instructions": alg_inst, "frac": alg_inst / slots, "inst_alg": ia,
                           "definition": "(inst_alg,node * N_node + inst_alg,tri * N_tri + inst_alg,ray * N_ray) / 32 lanes / (148 SM x 4 schedulers x f_SM x kernel time)"})

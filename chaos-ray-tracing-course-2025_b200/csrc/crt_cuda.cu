@@ -39,7 +39,8 @@ struct crt_cuda_ctx {
     size_t off_lights = 0, off_materials = 0, off_textures = 0; // arena offsets of the small shading arrays (crt_cuda_update_shading)
     const char *warm_base = nullptr; // what a k-d walk reads: triangles .. walk tree .. leaf references, one range of the arena
     size_t warm_bytes = 0;
-    int warm_mode = -1;              // $CRT_WARM_L2: 0 never, 1 always, -1 by scene size
+    int warm_mode = -1;              // $CRT_WARM_L2: 0 never, 1 always (prefetches), 2 always (loads), -1 by scene size
+    bool warm_loads = false;
     int packet_mode = -1;        // primary level as warp packets (crt_trace_packet.cuh): -1 by pixels per triangle, 0 / 1 = $CRT_PACKET
     bool packet_primary = false; // this frame's decision
     crt_render_params last_params{};
@@ -222,8 +223,11 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     // the walk's working set on its way into L2 while the first kernels start (k_warm_l2, crt_push.cuh): pays when the
     // set is large enough to be fetched miss by miss otherwise, and small enough to stay
     if (params->traversal == CRT_TRAVERSAL_KD && ctx->warm_bytes > 0 &&
-        (ctx->warm_mode == 1 || (ctx->warm_mode < 0 && ctx->warm_bytes >= (size_t(4) << 20) && ctx->warm_bytes <= (size_t(120) << 20)))) {
-        k_warm_l2<<<148 * 4, 256, 0, ctx->stream>>>(ctx->warm_base, ctx->warm_bytes);
+        ctx->warm_mode == 1) { // off unless $CRT_WARM_L2 asks: measured (r2e, r2m), it does not pay
+        if (ctx->warm_loads)
+            k_warm_l2_loads<<<148 * 8, 256, 0, ctx->stream>>>(reinterpret_cast<const uint4 *>(ctx->warm_base), ctx->warm_bytes / 16, nullptr);
+        else
+            k_warm_l2<<<148 * 4, 256, 0, ctx->stream>>>(ctx->warm_base, ctx->warm_bytes);
         ++extra_launches;
     }
     // render_image cuts the frame into int(float(extent) / bucket_size + 0.5) buckets per axis, the last one absorbing
@@ -595,7 +599,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     ctx->warm_base = ctx->d_arena, ctx->warm_bytes = warm_end;
     ctx->warm_mode = -1;
     if (const char *k = std::getenv("CRT_WARM_L2"); k && *k)
-        ctx->warm_mode = *k == '1' ? 1 : 0;
+        ctx->warm_mode = (*k == '1' || *k == '2') ? 1 : 0, ctx->warm_loads = *k == '2';
     if (const char *k = std::getenv("CRT_WALKER"); k && *k)
         ctx->wf.classic_walker = std::strcmp(k, "classic") == 0;
     ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)

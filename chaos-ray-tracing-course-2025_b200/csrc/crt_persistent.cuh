@@ -159,7 +159,9 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         const unsigned parked = __ballot_sync(full, parked0 >= 0);
         const unsigned walkers = __ballot_sync(full, (ply >= 0 || helper) && !w.done() && !blocked);
         const unsigned waiting = __ballot_sync(full, (ply >= 0 || helper) && w.done() && parked0 >= 0);
-        const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_N_WAITERS);
+        // (once the queue is empty nothing is gained by batching: see k_wf_trace_lean)
+        const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u ||
+                                           __popc(waiting) >= (exhausted ? 1 : CRT_N_WAITERS));
         if (fire) {
             lean_test_parked<STATS>(S, ws, lane, src, parked0, parked1, cn);
             parked0 = -1, parked1 = -1;
@@ -176,7 +178,9 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         const unsigned ready_m = __ballot_sync(full, ready);
         const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && !w.done());
         patience = ready_m != 0u ? patience + 1 : 0;
-        if (ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u || patience >= (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE))) {
+        // (with the queue empty a ready lane continues at once: its pixel's remaining bounces are the critical path)
+        if (ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u ||
+                              patience >= (exhausted && !GI ? 1 : (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE)))) {
             patience = 0;
             if (ready) {
                 int act = 0; // 0: consume the finished query, 1: shade_ray(ray, depth) entry, 2: return c to the callers

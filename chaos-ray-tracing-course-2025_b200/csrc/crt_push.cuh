@@ -31,4 +31,16 @@ __global__ void __launch_bounds__(256) k_warm_l2(const char *__restrict__ base, 
         asm volatile("prefetch.global.L2 [%0];" ::"l"(base + i * 128));
 }
 
+// The same with real loads (ld.global.cg: cached in L2, not in L1): a prefetch may be dropped when the memory system is
+// busy, a load cannot.  `sink` is never written (the xor of 16-byte words of scene data is not the magic value).
+__global__ void __launch_bounds__(256) k_warm_l2_loads(const uint4 *__restrict__ base, size_t words, unsigned *__restrict__ sink) {
+    unsigned acc = 0;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < words; i += size_t(gridDim.x) * blockDim.x) {
+        const uint4 v = __ldcg(base + i);
+        acc ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+    if (acc == 0x9e3779b9u && sink)
+        *sink = acc;
+}
+
 } // namespace crtdev

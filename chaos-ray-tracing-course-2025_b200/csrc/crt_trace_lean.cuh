@@ -268,7 +268,11 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_N_MINBLOCKS) k_wf_trace_lean(
         const unsigned parked = __ballot_sync(full, parked0 >= 0);
         const unsigned walkers = __ballot_sync(full, (my >= 0 || helper) && !w.done() && !blocked);
         const unsigned waiting = __ballot_sync(full, (my >= 0 || helper) && w.done() && parked0 >= 0);
-        const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u || __popc(waiting) >= CRT_N_WAITERS);
+        // batching the tests buys SIMD width while rays keep coming; once the queue is empty what is left is a chain of
+        // dependent work per lane (r2d: one rank's share of an 8-rank frame is all tail), and a lane that only waits
+        // for its tests is tested at once
+        const bool fire = parked != 0u && (__popc(parked) >= CRT_N_TRIGGER || __any_sync(full, blocked) || walkers == 0u ||
+                                           __popc(waiting) >= (exhausted ? 1 : CRT_N_WAITERS));
         if (fire) {
             lean_test_parked<STATS>(S, ws, lane, src, parked0, parked1, cn);
             parked0 = -1, parked1 = -1;

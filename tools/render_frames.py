@@ -27,7 +27,14 @@ flat = r.upload(scene.flatten(reference_tree=traversal == "literal"))
 part = dict(rank=int(os.environ["CRT_RANK"]), world=int(os.environ["CRT_WORLD"]), band_rows=8) if os.environ.get("CRT_WORLD") else {}
 p = crt.default_params(max_ray_depth=depth, collect_stats=stats, **part,
                        pipeline={"auto": 0, "mega": 1, "wavefront": 2, "persistent": 3, "hybrid": 4}[pipeline], traversal={"kd": 1, "literal": 0}[traversal])
+flush = None
+if os.environ.get("CRT_FLUSH") == "1":  # cold L2 before every frame, as bench.py's timed steps have it
+    import torch
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
 for i in range(frames):
+    if flush is not None:
+        flush.fill_(i & 0xFF)
+        torch.cuda.synchronize()
     _, _, st = r.render(p, want_rgb=False, want_rgb8=False)
     print(workload, pipeline, traversal, "frame", i, {k: v for k, v in st.items() if v and k != "pad"})
 r.close()
