@@ -10,11 +10,7 @@
 
 #include "crt_kernels.cuh"
 #include "crt_wavefront.cuh"
-#ifndef CRT_PERSIST_CLASSIC
 #include "crt_persistent.cuh"
-#else
-#include "crt_persistent_classic.cuh" // round 1's walker inside the persistent kernel (A/B builds only)
-#endif
 #include "crt_ppm.cuh"
 #include "crt_push.cuh"
 #include "crt_gi.h"
@@ -35,7 +31,7 @@ struct crt_cuda_ctx {
     bool have_scene = false;
     bool has_secondary = false; // some material can spawn reflection / refraction rays
     int bucket_size = 0;        // Scene::bucket_size: only decides whether the frame gets any bucket at all (enqueue_frame)
-    bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_light (crt_trace_light.cuh)
+    bool light_leaves = false;  // walk tree with a few triangles per leaf: k_wf_trace_lean (crt_trace_lean.cuh)
     size_t off_lights = 0, off_materials = 0, off_textures = 0; // arena offsets of the small shading arrays (crt_cuda_update_shading)
     const char *warm_base = nullptr; // what a k-d walk reads: triangles .. walk tree .. leaf references, one range of the arena
     size_t warm_bytes = 0;
@@ -600,8 +596,6 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     ctx->warm_mode = -1;
     if (const char *k = std::getenv("CRT_WARM_L2"); k && *k)
         ctx->warm_mode = (*k == '1' || *k == '2') ? 1 : 0, ctx->warm_loads = *k == '2';
-    if (const char *k = std::getenv("CRT_WALKER"); k && *k)
-        ctx->wf.classic_walker = std::strcmp(k, "classic") == 0;
     ctx->packet_mode = -1; // decided per frame from the image size (enqueue_frame)
     if (const char *k = std::getenv("CRT_PACKET"); k && *k)
         ctx->packet_mode = *k == '1' ? 1 : 0;

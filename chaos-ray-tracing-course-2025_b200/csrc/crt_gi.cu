@@ -8,11 +8,7 @@
 #define crtdev crtdev_gi
 #include "crt_kernels.cuh"
 #include "crt_wavefront.cuh"
-#ifndef CRT_PERSIST_CLASSIC
 #include "crt_persistent.cuh"
-#else
-#include "crt_persistent_classic.cuh" // round 1's walker inside the persistent kernel (A/B builds only)
-#endif
 #undef crtdev
 
 #include "crt_gi.h"

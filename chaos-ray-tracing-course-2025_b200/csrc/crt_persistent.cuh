@@ -2,7 +2,7 @@
 // recursion of shade_ray (src/core/crt_renderer.cpp:46-145), depth-first with the explicit frame stack of
 // k_render_mega (crt_kernels.cuh) -- so evaluation order, RNG order (one PCG32 stream per pixel, crt_random.h) and
 // the nesting in which colours are combined are the reference's -- while the closest-hit queries are served by the
-// warp-cooperative walk of k_wf_trace_light: speculative walk, leaves parked and tested warp-wide, work stealing.
+// warp-cooperative walk of k_wf_trace_lean: speculative walk, leaves parked and tested warp-wide, work stealing.
 //
 // Why (ncu r1p): the level-synchronous wavefront pays one tail per bounce level (levels 2-8 of C4 hold
 // 18 % of the rays and take 55 % of the frame) and cannot run GI at all; the per-pixel megakernel can, but its lanes
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
     bool shadow_q = false; // the running query is a shadow ray of frames[depth]'s light loop, not a shade_ray call
     Pcg32 rng{};
     Frame frames[kMaxDepthCap + 1];
-    // ---- walk state (see k_wf_trace_light)
+    // ---- walk state (see k_wf_trace_lean)
     int parked0 = -1, parked1 = -1; // parked leaves (node ids)
     bool exhausted = false;
     unsigned src = lane;

@@ -69,8 +69,6 @@ struct __align__(16) TraceWarpShared {
 // shared memory ([entry][lane]: conflict-free), older ones are spilled to local memory and rarely read back.
 constexpr uint32_t kFlagBit = 0x80000000u; // entry pushed for a ray lying IN the split plane: its interval starts at 0
 
-constexpr int kStolenNode = 0x7FFFFFFF; // stack entry whose subtree a helper lane has taken over
-
 struct TraceWalker {
     float tmin, tmax, root_tmax;
     int node; // node to visit next, or -1 when the walk is finished
@@ -147,42 +145,6 @@ struct TraceWalker {
         }
         if (STATS)
             ++cn.node_tests;
-    }
-
-    // Bare pop for k_wf_trace_light / k_render_persistent: take the top entry, nothing else.  Whether that subtree can
-    // still hold a closer hit is decided when it is VISITED (prune_at_visit), in the instruction stream all lanes
-    // share, instead of here, where ~4 of 32 lanes are active (ncu r1s: the pruning pop was 23 % of the issued
-    // instructions at 3.9 threads per instruction).
-    template <bool STATS, class WS>
-    __device__ __forceinline__ void pop_fast(WS &ws, uint2 *spill, unsigned lane, Counters &cn) {
-        const bool empty = sp == 0; // nothing pending: the walk is over (the loads below then read slot -1 & 7, unused)
-        sp -= empty ? 0 : 1;
-        uint2 e = ws.stack[sp & (kWin - 1)][lane];
-        float below = __uint_as_float(ws.stack[(sp - 1) & (kWin - 1)][lane].y);
-        if (__builtin_expect(!empty & (sp <= lo), 0)) { // rare: the entry or the one below it was spilled
-            if (sp < lo)
-                e = spill[sp], lo = sp;
-            if (sp > 0)
-                below = __uint_as_float(entry_at(ws, spill, lane, sp - 1).y);
-        }
-        tmax = sp == 0 ? root_tmax : below;
-        const bool flag = !empty & ((e.x & kFlagBit) != 0u);
-        flagged -= flag ? 1 : 0;
-        tmin = flag ? 0.0f : __uint_as_float(e.y);
-        node = empty ? -1 : int(e.x & ~kFlagBit);
-        if (STATS && !empty)
-            ++cn.node_tests;
-    }
-
-    // true: the node I am about to visit cannot hold a closer (or equal) hit, or a helper has taken it over -- pop
-    // instead.  When it is pruned with a wide margin and no in-plane entry is pending, everything on the stack is
-    // pruned as well (see pop()): the walk is over.
-    __device__ __forceinline__ bool prune_at_visit(float best_t) {
-        const bool taken = node == kStolenNode;
-        const bool pruned = tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best_t;
-        if (pruned & !taken & (flagged == 0) & (tmin - (fabsf(tmin) * 1e-3f + 1e-4f) > best_t))
-            sp = 0, lo = 0;
-        return pruned | taken;
     }
 
     // ONE node of the walk: true when `n` is a leaf.  Same decisions as KdWalker::step, written as selects so that

@@ -1,14 +1,24 @@
-// TRACE stage, round 2: k_wf_trace_light's organisation (persistent warps, lane-level ray replacement, leaves parked
-// in two register slots and tested warp-wide, work stealing at the end of a level) around the LEAN walker of
-// crt_walk_lean.h.  Included by crt_wavefront.cuh after crt_trace_light.cuh.
+// TRACE stage for walk trees with LIGHT leaves (the SAH tree of core/crt_kdbuild.cpp: ~2 triangles per leaf, hardly any
+// triangle referenced twice): closest hit of every ray of one bounce level.  Included by crt_wavefront.cuh after
+// crt_trace.cuh (whose k_wf_trace serves walk trees with heavy leaves, $CRT_WALK_TREE=reference).
+// Replaces ray_intersect_acceleration_tree + ray_intersect_triangle (src/core/crt_intersection.cpp:109-136, :47-93).
 //
-// What changed against k_wf_trace_light and why (ncu r1zz: 138 SASS instructions per node visit at 77-79 % issue-slot
-// utilisation, 19 of 32 lanes active -- the kernel is bound by the instructions of a visit):
-//   * the visit itself: crt_walk_lean.h (direction-sign child order, sentinel stack entry, NaN-driven in-plane case);
-//   * pruning is ONE comparison per visit, tmin > best + slack with the threshold computed once per round; the
-//     wide-margin "everything pending is pruned" test runs only for lanes that were pruned;
-//   * a subtree a helper lane took over is replaced in the victim's stack by the scene's EMPTY LEAF (a real node the
-//     upload appends to the walk tree), so a visit never asks whether its node was stolen;
+// With such a tree a ray takes ~25-65 node visits but only 1-4 leaf visits and 1-6 triangle tests.  Organisation:
+//   * persistent warps; a lane owns one ray at a time, idle lanes take the next rays of the level's queue (one atomicAdd
+//     per warp) when fewer than CRT_N_REFILL lanes are busy;
+//   * the walk is crt_walk_lean.h, one straight-line iteration per node visit for all walking lanes (round 2: 95 SASS
+//     instructions per visit instead of 138);
+//   * a lane that reaches a leaf PARKS it (its node id, two register slots) and walks on -- speculatively: the leaf's
+//     triangles have not been tested yet, so the distance used for pruning may be stale, never wrong;
+//   * when enough leaves are parked (or a lane has both slots full, or nobody can walk) the warp runs ONE test phase:
+//     shfl prefix sum of the parked triangle counts, owner lane by binary search, every lane tests whichever
+//     (ray, triangle) pair comes next, branch-free; hits merge through a 64-bit shared atomicMin on (t bits, triangle) =
+//     the reference's winner rule (closest, ties to the lowest parse index).  A triangle referenced from two leaves is
+//     simply tested twice;
+//   * when the level's queue is empty, idle lanes take over the bottom stack entries (the farthest pending subtrees) of
+//     lanes that still walk; the victim finds the scene's EMPTY LEAF in that entry's place (a real node the upload
+//     appends to the walk tree), so a visit never asks whether its node was stolen.  From then on tests run as soon as a
+//     lane waits for them (step 22): what is left is a chain of dependent work per lane;
 //   * node visits are counted where the node is loaded (STATS builds).
 #pragma once
 
@@ -35,14 +45,27 @@ namespace crtdev {
 #define CRT_PREFETCH_PUSH 0
 #endif
 
+// per-warp state in shared memory ([entry][lane] layouts: conflict-free)
+struct __align__(16) LightWarpShared {
+    float ray[9][32];            // origin xyz, direction xyz, 1/direction xyz of each lane's ray
+    unsigned long long best[32]; // (float bits of t) << 32 | triangle index
+    uint2 stack[kWin][32];       // {node | kFlagBit, entry distance bits}
+    int helpers[32];             // lanes currently walking a stolen subtree of this lane's ray
+};
+
 static_assert(crtwalk::kWin == kWin, "stack window of the lean walker and of LightWarpShared");
 
 __device__ __forceinline__ crtwalk::Node as_walk_node(const int4 n) { return crtwalk::Node{ n.x, n.y, n.z, n.w }; }
 
 // ---- pieces shared with k_render_persistent -----------------------------------------------------------------------
 
-// idle lanes take over the bottom stack entries (the farthest pending subtrees) of lanes that still walk; see
-// k_wf_trace_light for the protocol.  `busy_lane` = this lane owns a ray or helps one; returns through the references.
+// Idle lanes take over the bottom stack entries (the farthest pending subtrees) of lanes that still walk.  A level ends
+// with its longest ray; a skimming ray crosses ~1000 cells one dependent load at a time, and this spreads that walk over
+// the warp.  Thieves and victims are paired by rank among their ballots; the thief reads the victim's entry {node, exit}
+// (its interval starts where the entry above it ends) and walks it against the victim's ray (`src`); the victim's entry
+// becomes a tombstone -- the empty leaf -- that keeps its exit distance for the entries above it; hits merge through the
+// owner's ws.best as always, and the owner retires only when ws.helpers says nobody walks for it any more.
+// owns_work = this lane owns a ray (or pixel); results come back through the references.
 template <bool STATS>
 __device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWalker &w, unsigned lane, unsigned lt_mask, bool owns_work, bool &helper,
                                            unsigned &src, int &stolen, uint32_t empty_leaf, Counters &cn) {

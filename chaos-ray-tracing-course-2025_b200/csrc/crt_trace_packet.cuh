@@ -1,6 +1,6 @@
 // PRIMARY level as warp packets: one warp = one 8x4 pixel patch = 32 camera rays that share their origin and walk
-// the tree TOGETHER.  Included by crt_wavefront.cuh after crt_trace_light.cuh; replaces k_wf_raygen + the level-0
-// launch of k_wf_trace_light (CRT_TRAVERSAL_KD; $CRT_PACKET=0 keeps those).
+// the tree TOGETHER.  Included by crt_wavefront.cuh after crt_trace_lean.cuh; replaces k_wf_raygen + the level-0
+// launch of k_wf_trace_lean (CRT_TRAVERSAL_KD; $CRT_PACKET=0 keeps those).
 //
 // Why: the per-lane walk treats the 32 rays of a warp as unrelated -- every lane loads its own node, keeps its own
 // stack in shared memory, and the lanes drift apart (ncu r1z, level 0: 19.5 of 32 threads per instruction, ~120 thread

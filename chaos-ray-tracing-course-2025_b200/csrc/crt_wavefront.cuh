@@ -76,7 +76,6 @@ struct WavefrontState {
     int *h_flags = nullptr;   // pinned: {overflow, pend_hi, pend_lo_inv} of the last frame ...
     int *h_count = nullptr;   // ... and its rays per level (WfCtl::count): what a pool that overflowed is re-sized from
     double grow = 1.0;        // pool = grow * pixels
-    bool classic_walker = false; // $CRT_WALKER=classic
 };
 
 enum NodeKind : int { kTerminal = 0, kNodeReflect = 1, kNodeRefract = 2, kNodeTir = 3 };
@@ -170,7 +169,6 @@ __device__ __forceinline__ void write_ray(const DScene &S, const WfBuffers &b, i
 // ------------------------------------------------------------------------------------------------ TRACE
 } // namespace crtdev
 #include "crt_trace.cuh"
-#include "crt_trace_light.cuh"
 #include "crt_trace_lean.cuh"
 #include "crt_trace_packet.cuh"
 namespace crtdev {
@@ -373,9 +371,7 @@ inline void wavefront_free(WavefrontState &w) {
     cudaFree(w.b.ray_o), cudaFree(w.b.ray_d), cudaFree(w.b.ray_i), cudaFree(w.b.ray0_d), cudaFree(w.b.ray0_i), cudaFree(w.b.ray0_slot), cudaFree(w.b.hit), cudaFree(w.b.rec), cudaFree(w.b.alb), cudaFree(w.b.col), cudaFree(w.b.pend),
         cudaFree(w.b.ctl);
     cudaFreeHost(w.h_flags);
-    const bool classic = w.classic_walker;
     w = WavefrontState{};
-    w.classic_walker = classic;
 }
 
 inline cudaError_t wavefront_reserve(WavefrontState &w, int P, bool secondary) {
@@ -451,12 +447,7 @@ template <int TRAV>
 inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, const DParams &dp, bool stats, int level, int blocks, Counters *counters,
                                    cudaStream_t stream, bool light) {
     if (TRAV == CRT_TRAVERSAL_KD && light) {
-        if (w.classic_walker) { // $CRT_WALKER=classic: round 1's k_wf_trace_light, kept for A/B measurements
-            if (stats)
-                k_wf_trace_light<true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
-            else
-                k_wf_trace_light<false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
-        } else if (stats)
+        if (stats)
             k_wf_trace_lean<true><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
         else
             k_wf_trace_lean<false><<<blocks, kTraceBlock, 0, stream>>>(S, dp, w.b, level, counters);
@@ -469,7 +460,7 @@ inline void wavefront_launch_trace(const WavefrontState &w, const DScene &S, con
 }
 
 // `secondary` = the scene can spawn reflection / refraction rays at all (known from its materials on the host)
-// `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_light instead of k_wf_trace
+// `light_leaves` = the walk tree's leaves hold a few triangles each (SAH tree): k_wf_trace_lean instead of k_wf_trace
 inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DParams &dp, int traversal, bool stats, bool secondary, float *rgb,
                                     uint8_t *rgb8, Counters *counters, cudaStream_t stream, int *launches, bool light_leaves,
                                     int first_levels_only = 0, cudaEvent_t after_primary = nullptr, bool packet_primary = false) {
@@ -486,7 +477,7 @@ inline cudaError_t wavefront_render(WavefrontState &w, const DScene &S, const DP
     // evaluates the subtrees of the queued level-L rays (k_render_persistent<SEEDED>) and runs the resolves of levels L-1 .. 0
     const int all_levels = secondary ? int(dp.max_ray_depth) + 1 : 1;
     const int levels = first_levels_only > 0 ? min(first_levels_only, all_levels) : all_levels;
-    const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? (w.classic_walker ? CRT_L_MINBLOCKS : CRT_N_MINBLOCKS) : 8);
+    const int trace_blocks = w.sm_count * (light_leaves && traversal == CRT_TRAVERSAL_KD ? CRT_N_MINBLOCKS : 8);
     int n = 0;
     // primary level of the k-d walk as warp packets (crt_trace_packet.cuh): ray generation, root-box entry and the walk
     // of a whole 8x4 patch in one kernel, no ray records
