@@ -400,13 +400,18 @@ def run_ours(args):
     def frame_index(step):  # c5: a different orbit frame on every rank, every step
         return orbit_frame(step * world + rank, len(orbit))
 
+    cameras = {}  # built once: the timed loop should launch kernels, not assemble ctypes structures
+
     def camera_for(step):
-        cam = crt.Camera.from_buffer_copy(flat.camera)
-        if orbit is not None:
-            pos, mat = orbit[frame_index(step)]
-            cam.position[:] = [float(v) for v in pos]
-            cam.rotation[:] = [float(v) for v in mat]
-        return cam
+        key = frame_index(step) if orbit is not None else -1
+        if key not in cameras:
+            cam = crt.Camera.from_buffer_copy(flat.camera)
+            if orbit is not None:
+                pos, mat = orbit[key]
+                cam.position[:] = [float(v) for v in pos]
+                cam.rotation[:] = [float(v) for v in mat]
+            cameras[key] = cam
+        return cameras[key]
 
     # --- ray / test counts of the timed configuration (counting build of the same kernels, outside the timed region)
     counted = {"rays": 0, "node_tests": 0, "tri_tests": 0, "entered_rays": 0}
