@@ -19,7 +19,9 @@ struct KdBuildStats {
 struct KdBuildParams {
     float c_node{ 1.0f };  // cost of one node step of the trace kernel (the unit)
     float c_leaf{ 1.0f };  // fixed cost of parking a leaf for the next test phase
-    float c_tri{ 1.5f };   // cost per tested triangle (swept on B200 with k_wf_trace_light, tools/sah_sweep.sh)
+    float c_tri{ 1.0f };   // cost per tested triangle.  Swept on B200 again with the lean kernels (tools/gpu_sah.sh,
+                           // profiles/r2p_*): node visits are what the latency-bound walk pays for, tests run warp-wide --
+                           // 1.5 -> 1.0: C4 2.82 -> 2.77 ms, one rank's share of an 8-rank frame 0.88 -> 0.80 ms, GI 156.4 -> 154.8 ms
     float empty_bonus{ 1.0f }; // < 1 favours splits that cut away empty space; the sweep on B200 found no gain from it
     int max_depth{ 44 };   // device stack: fast_max_depth + 2 <= kStack (48)
     int exact_below{ 96 }; // nodes with at most this many triangles sweep every triangle bound; larger ones use bins
