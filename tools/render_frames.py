@@ -24,7 +24,7 @@ scene = crt.Scene.load_json(text, root)
 r = crt.Renderer(0)
 flat = r.upload(scene.flatten(reference_tree=traversal == "literal"))
 # CRT_RANK / CRT_WORLD: render only the row bands rank r of an N-rank job owns (what each GPU of a tile-sharded frame does)
-part = dict(rank=int(os.environ["CRT_RANK"]), world=int(os.environ["CRT_WORLD"]), band_rows=8) if os.environ.get("CRT_WORLD") else {}
+part = dict(rank=int(os.environ["CRT_RANK"]), world=int(os.environ["CRT_WORLD"]), band_rows=int(os.environ.get("CRT_BAND", "8"))) if os.environ.get("CRT_WORLD") else {}
 p = crt.default_params(max_ray_depth=depth, collect_stats=stats, **part,
                        pipeline={"auto": 0, "mega": 1, "wavefront": 2, "persistent": 3, "hybrid": 4}[pipeline], traversal={"kd": 1, "literal": 0}[traversal])
 flush = None
