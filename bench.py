@@ -465,13 +465,19 @@ def run_ours(args):
         C5 frame take the host 0.65 ms that way, the device 0.31 ms).  Returns per-step ms."""
         begin = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
         end = [torch.cuda.Event(enable_timing=True) for _ in range(n)]
+        t0 = time.perf_counter()
         for s in range(n):
             flush.fill_(s & 0xFF)
             begin[s].record(stream)
             device_step(first_step + s)
             end[s].record(stream)
+        t1 = time.perf_counter()
         torch.cuda.synchronize(device)
+        t2 = time.perf_counter()
         renderer.synchronize()  # (the context's own bookkeeping: ray-pool flags of the last frame)
+        # how long the host took to ISSUE a step, and a step's share of the wall clock until the device was done: when
+        # the two are equal the host is the limit and the device's brackets contain the gaps between its launches
+        timed_steps.host = {"issue_ms_per_step": (t1 - t0) / n * 1e3, "wall_ms_per_step": (t2 - t0) / n * 1e3}
         return [b.elapsed_time(e) for b, e in zip(begin, end)]
 
     sampler = ClockSampler(local) if rank == 0 else None  # (before the barrier: NVML start-up on rank 0 must not delay its first timed step)
@@ -489,7 +495,7 @@ def run_ours(args):
     total_ms = all_max(sum(step_ms))
     clocks = sampler.window(wall0, wall1) if sampler else None
     per_rank = [None] * world  # every rank's own view of its steps (the line reports the slowest rank)
-    mine = {"rank": rank, "ms_mean": statistics.mean(step_ms), "ms_min": min(step_ms), "ms_median": statistics.median(step_ms), "ms_max": max(step_ms)}
+    mine = {"rank": rank, **timed_steps.host, "ms_mean": statistics.mean(step_ms), "ms_min": min(step_ms), "ms_median": statistics.median(step_ms), "ms_max": max(step_ms)}
     if world > 1:
         dist.all_gather_object(per_rank, mine)
     else:
