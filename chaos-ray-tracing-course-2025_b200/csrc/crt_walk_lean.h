@@ -39,7 +39,10 @@ namespace crtwalk {
 
 constexpr uint32_t kFlagBit = 0x80000000u; // stack entry pushed for a ray lying IN the split plane: its interval starts at 0
 constexpr int kDone = 0x7FFFFFFE;          // node id of the sentinel entry: the walk is over
-constexpr int kWin = 8;                    // top-of-stack window per lane in shared memory; older entries spill
+#ifndef CRT_WIN
+#define CRT_WIN 8
+#endif
+constexpr int kWin = CRT_WIN;              // top-of-stack window per lane in shared memory; older entries spill
 
 struct Node {   // crt_kd_node as the kernels load it: {split bits, a, b, axis} / {0, first, count, 3}
     int32_t x, y, z, w;
