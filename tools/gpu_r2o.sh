@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2, pass o (8 GPUs): bench.py as the driver launches it -- C4 at N = 8, 4, 2; 15-01/scene2 with GI and the C5
 # orbit at N = 8; the hybrid hand-over level for one rank's share of an 8-rank frame
-tag=${1:-r2o}
+tag=${1:-r2t}
 mkdir -p gpurun_out
 run() { # n workload
   local n=$1 w=$2; shift 2
