@@ -105,18 +105,18 @@ def orbit_of(text: str, frames: int = 240):
 
 
 def orbit_frame(k: int, frames: int = 240) -> int:
-    """the k-th frame a job renders.  The orbit is walked in steps of 7 frames (coprime to 240: every frame comes up once
-    in 240) so that a run of 20 steps samples the whole circle whatever N is -- the frames near the scene file's own
-    camera cost twice the orbit's average (r2l: 0.65 ms against 0.31 ms), and a 1-GPU run that only ever saw those would
-    be compared with an 8-GPU run that saw 160 others."""
-    return (7 * k) % frames
+    """the k-th frame a job renders.  The orbit is walked in steps of 97 frames (coprime to 240: every frame comes up once
+    in 240) so that a run of 20 steps samples the WHOLE circle whatever N is: a frame costs between 0.15 and 0.65 ms
+    depending on where the camera stands (r2l, r2t: the half of the circle a stride of 7 gave a 1-GPU run averages 0.19 ms,
+    the frames an 8-rank run saw 0.29 ms -- on the same single GPU), and a scaling figure must not compare two arcs."""
+    return (97 * k) % frames
 
 
 def partition_text(workload: str, world: int, partition: str, gather: str) -> str:
     if world <= 1:
         return "single GPU"
     if partition == "frames":
-        return ("orbit: the k-th frame of the job (orbit frame 7k mod 240) -> rank k % N, every rank renders a different frame per step, no exchange" if workload == "c5"
+        return ("orbit: the k-th frame of the job (orbit frame 97k mod 240) -> rank k % N, every rank renders a different frame per step, no exchange" if workload == "c5"
                 else "REPLICAS: every rank renders the same whole frame, no exchange (not a scaling measurement of one frame)")
     return f"one frame in interleaved row bands of {BAND_ROWS}, " + ("pushed into rank 0's frame by peer stores over NVLink + 1-element all-reduce as the barrier"
                                                                        if gather == "peer" else "NCCL gather of u8 rgb to rank 0")
@@ -398,7 +398,10 @@ def run_ours(args):
     params = crt.default_params(**common, **part)
 
     def frame_index(step):  # c5: a different orbit frame on every rank, every step
-        return orbit_frame(step * world + rank, len(orbit))
+        # ($CRT_ORBIT_AS=rank/world: the frame sequence of that rank of a larger job, on this GPU -- a measurement aid)
+        fake = os.environ.get("CRT_ORBIT_AS")
+        r_, w_ = (int(v) for v in fake.split("/")) if fake else (rank, world)
+        return orbit_frame(step * w_ + r_, len(orbit))
 
     cameras = {}  # built once: the timed loop should launch kernels, not assemble ctypes structures
 
