@@ -23,6 +23,7 @@ TRAVERSAL_LITERAL, TRAVERSAL_KD, TRAVERSAL_BRUTE = 0, 1, 2
 FLATTEN_REFERENCE_TREE = 1
 PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_PERSISTENT, PIPELINE_HYBRID = 0, 1, 2, 3, 4
 REF_CULL_BIT = 0x80000000
+PPM_NOALLOC_MAX_PIXELS = 8388608  # CRT_PPM_NOALLOC_MAX_PIXELS (include/crt_cuda.h)
 
 # every symbol include/crt_cuda.h declares (tests check that the library exports each of them)
 EXPORTED_SYMBOLS = [
@@ -30,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "crt_scene_free", "crt_scene_last_error", "crt_render_params_default", "crt_cuda_device_count", "crt_cuda_create",
     "crt_cuda_destroy", "crt_cuda_last_error", "crt_cuda_set_stream", "crt_cuda_upload_scene", "crt_cuda_pack_walk_tree", "crt_cuda_walk_node_bytes", "crt_cuda_set_camera", "crt_cuda_update_shading", "crt_cuda_group_update_shading",
     "crt_cuda_render", "crt_cuda_render_frame", "crt_cuda_render_device", "crt_cuda_device_framebuffer", "crt_cuda_synchronize",
-    "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device",
+    "crt_cuda_primary_hits", "crt_cuda_primary_rays", "crt_cuda_encode_ppm", "crt_cuda_encode_ppm_device", "crt_cuda_encode_ppm_noalloc",
     "crt_cuda_frame_create", "crt_cuda_frame_open", "crt_cuda_frame_attach", "crt_cuda_frame_pointer", "crt_cuda_push_bands",
     "crt_cuda_group_create", "crt_cuda_group_destroy", "crt_cuda_group_last_error", "crt_cuda_group_size", "crt_cuda_group_upload_scene",
     "crt_cuda_group_set_camera", "crt_cuda_group_render", "crt_cuda_group_frame", "crt_cuda_group_encode_ppm",
@@ -138,6 +139,7 @@ def _load_library():
         "crt_cuda_primary_rays": (C.c_int, [vp, vp]),
         "crt_cuda_encode_ppm": (C.c_int, [vp, vp, C.c_size_t, P(C.c_size_t)]),
         "crt_cuda_encode_ppm_device": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_size_t, P(C.c_size_t)]),
+        "crt_cuda_encode_ppm_noalloc": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_size_t, P(C.c_size_t)]),
         "crt_cuda_frame_create": (C.c_int, [vp, C.c_int, C.c_int, vp]),
         "crt_cuda_frame_open": (C.c_int, [vp, vp, C.c_int, C.c_int]),
         "crt_cuda_frame_attach": (C.c_int, [vp, vp, C.c_int, C.c_int]),
@@ -363,6 +365,15 @@ class Renderer:
         buf = C.create_string_buffer(length.value)
         self._check(lib.crt_cuda_encode_ppm_device(self._ctx, C.c_void_p(rgb8_ptr), width, height, buf, length.value, C.byref(length)), "crt_cuda_encode_ppm_device")
         return buf.raw[: length.value]
+
+    def encode_ppm_noalloc(self, rgb8_ptr: int, width: int, height: int, text_ptr: int, capacity: int) -> int:
+        """P3 text of a quantised device frame written into the CALLER's device buffer; allocates nothing (static device
+        scratch, at most PPM_NOALLOC_MAX_PIXELS pixels; calls that overlap on the GPU race).  Returns the text length;
+        text_ptr = 0 only queries it."""
+        length = C.c_size_t()
+        self._check(lib.crt_cuda_encode_ppm_noalloc(self._ctx, C.c_void_p(rgb8_ptr), width, height, C.c_void_p(text_ptr or None), capacity, C.byref(length)),
+                    "crt_cuda_encode_ppm_noalloc")
+        return length.value
 
     def close(self):
         if self._ctx:

@@ -1235,3 +1235,69 @@ int crt_debug_tail(unsigned long long *out /* 16*40 */, int reset) {
 #endif
 
 } // extern "C"
+
+// ---- crt_cuda_encode_ppm_noalloc: the P3 encoder for callers that must not allocate ---------------------------------
+// (no counterpart in the reference -- include/crt_cuda.h)
+//
+// The encoder's scratch -- the text bytes of every block of kPpmBlockPixels pixels, then their prefix sums -- lives in
+// the file-scope device array below instead of ctx->d_scan, and the text goes straight into the CALLER's device buffer
+// instead of ctx->d_text: the call issues three kernels and one 8-byte copy and allocates nothing.  Every GPU that
+// loads the library holds the array (64 KiB + 64 B) until the process exits.  All calls on a device share it and it
+// keeps the last call's contents: nothing in it has to start at zero (k_ppm_lengths writes entries [0, n_blocks),
+// k_ppm_scan entry [n_blocks], before anything reads them -- so there is nothing to clear), but two calls that overlap
+// on the GPU (different streams, different threads) race on it.
+namespace {
+
+constexpr int kPpmNoAllocMaxBlocks = 8192;                                            // of kPpmBlockPixels (1024) pixels each
+constexpr size_t kPpmNoAllocMaxPixels = size_t(kPpmNoAllocMaxBlocks) * kPpmBlockPixels; // 8 388 608: a 3840x2160 frame fits
+constexpr int kNoAllocMaxDevices = 64;
+static_assert(kPpmNoAllocMaxPixels == CRT_PPM_NOALLOC_MAX_PIXELS, "the limit include/crt_cuda.h states");
+
+static __device__ __align__(256) unsigned long long g_ppm_noalloc_scratch[kPpmNoAllocMaxBlocks + 8];
+
+// In host code `g_ppm_noalloc_scratch` is the host-side stand-in of the symbol, not an address a kernel can use: the
+// device address is asked for once per device, with that device current, and kept here.
+unsigned long long *g_ppm_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+} // namespace
+
+extern "C" int crt_cuda_encode_ppm_noalloc(crt_cuda_ctx *ctx, const void *rgb8_dev, int width, int height, void *text_dev, size_t capacity,
+                                           size_t *length) {
+    if (!ctx)
+        return CRT_ERR_INVALID;
+    if (!rgb8_dev || width <= 0 || height <= 0)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm_noalloc needs a device frame with positive dimensions");
+    const size_t pixels = size_t(width) * size_t(height);
+    if (pixels > kPpmNoAllocMaxPixels)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm_noalloc: frame larger than the static scratch allows (8388608 pixels); use crt_cuda_encode_ppm_device");
+    if (ctx->device < 0 || ctx->device >= kNoAllocMaxDevices)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm_noalloc: device index beyond the 64 this entry point keeps an address for");
+    CRT_CK(ctx, cudaSetDevice(ctx->device));
+    unsigned long long *scratch = g_ppm_noalloc_ptr[ctx->device];
+    if (!scratch) { // set-up, once per device (the same address whichever thread asks first)
+        CRT_CK(ctx, cudaGetSymbolAddress(reinterpret_cast<void **>(&scratch), g_ppm_noalloc_scratch));
+        g_ppm_noalloc_ptr[ctx->device] = scratch;
+    }
+    PpmHeader header{};
+    header.length = std::snprintf(header.text, sizeof header.text, "P3\n%d %d\n255\n", width, height);
+    const int n_blocks = int((pixels + kPpmBlockPixels - 1) / kPpmBlockPixels);
+    const uint8_t *rgb8 = static_cast<const uint8_t *>(rgb8_dev);
+    k_ppm_lengths<<<n_blocks, kPpmThreads, 0, ctx->stream>>>(rgb8, pixels, width, scratch);
+    k_ppm_scan<<<1, 1024, 0, ctx->stream>>>(scratch, n_blocks);
+    CRT_CK(ctx, cudaGetLastError());
+    unsigned long long body = 0;
+    CRT_CK(ctx, cudaMemcpyAsync(&body, scratch + n_blocks, sizeof body, cudaMemcpyDeviceToHost, ctx->stream));
+    CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    const size_t total = size_t(header.length) + size_t(body);
+    if (length)
+        *length = total;
+    if (!text_dev)
+        return CRT_OK; // length query
+    if (capacity < total)
+        return fail(ctx, CRT_ERR_INVALID, "encode_ppm_noalloc: text buffer too small (query the length with text_dev = NULL)");
+    // k_ppm_format stores exactly text_dev[0, total): single bytes up to the first 16-byte boundary and after the last
+    k_ppm_format<<<n_blocks, kPpmThreads, 0, ctx->stream>>>(rgb8, pixels, width, scratch, header, static_cast<char *>(text_dev));
+    CRT_CK(ctx, cudaGetLastError());
+    CRT_CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}

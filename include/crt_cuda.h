@@ -283,6 +283,18 @@ int crt_cuda_encode_ppm(crt_cuda_ctx *ctx, char *text_out, size_t capacity, size
 /* same for any quantised frame in device memory (width*height*3 bytes, row 0 = top), e.g. the frame rank 0 holds
  * after the band gather of a multi-GPU render */
 int crt_cuda_encode_ppm_device(crt_cuda_ctx *ctx, const void *rgb8_dev, int width, int height, char *text_out, size_t capacity, size_t *length);
+/* The same encoder for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Calls no cudaMalloc / cudaFree or any allocating routine: the encoder's scratch (per-block text lengths and their
+ * prefix sums) is a file-scope `static __device__` array of CRT_PPM_NOALLOC_MAX_PIXELS / 1024 + 8 64-bit words (64 KiB,
+ * held by every GPU that loads the library until the process exits), and the text is written straight into the
+ * CALLER's device buffer text_dev[0, *length) (any alignment; capacity in bytes).  text_dev may be NULL to query the
+ * length.  width * height beyond CRT_PPM_NOALLOC_MAX_PIXELS is refused with CRT_ERR_INVALID (crt_cuda_last_error says
+ * why).  All calls on one device share the scratch array, which keeps the last call's contents (nothing in it has to
+ * start at zero: every word is written before it is read); calls that OVERLAP on the GPU race on it -- serialise them.
+ * Runs on the context's stream and returns after the text is complete. */
+#define CRT_PPM_NOALLOC_MAX_PIXELS 8388608 /* a 3840x2160 frame fits */
+int crt_cuda_encode_ppm_noalloc(crt_cuda_ctx *ctx, const void *rgb8_dev, int width, int height, void *text_dev, size_t capacity, size_t *length);
 
 #ifdef __cplusplus
 }
