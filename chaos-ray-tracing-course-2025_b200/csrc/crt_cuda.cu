@@ -36,6 +36,11 @@ struct crt_cuda_ctx {
     const char *warm_base = nullptr; // what a k-d walk reads: triangles .. walk tree .. leaf references, one range of the arena
     size_t warm_bytes = 0;
     int warm_mode = -1;              // $CRT_WARM_L2: 0 never, 1 always (prefetches), 2 always (loads), -1 by scene size
+    // $CRT_L2_PERSIST_MB > 0: that much of L2 set aside for persisting lines and the walk's working set (or only the
+    // tree and its references: $CRT_L2_WINDOW=tree) marked persisting on the launch stream (experiment, step 26)
+    size_t l2_window_offset = 0, l2_window_bytes = 0;
+    cudaStream_t l2_policy_stream = nullptr;
+    bool l2_policy_on = false;
     bool warm_loads = false;
     int packet_mode = -1;        // primary level as warp packets (crt_trace_packet.cuh): -1 by pixels per triangle, 0 / 1 = $CRT_PACKET
     bool packet_primary = false; // this frame's decision
@@ -182,6 +187,38 @@ void launch_persistent(crt_cuda_ctx *ctx, const DParams &dp, bool stats, bool gi
 #undef CRT_LAUNCH_P
 }
 
+// $CRT_L2_PERSIST_MB: the access policy window of the stream the frame is launched on (set once per stream and scene)
+int apply_l2_policy(crt_cuda_ctx *ctx) {
+    const char *mb = std::getenv("CRT_L2_PERSIST_MB");
+    const double want_mb = mb && *mb ? std::atof(mb) : 0.0;
+    if (want_mb <= 0.0 || ctx->l2_window_bytes == 0)
+        return CRT_OK;
+    if (ctx->l2_policy_on && ctx->l2_policy_stream == ctx->stream)
+        return CRT_OK;
+    int max_persist = 0, max_window = 0;
+    CRT_CK(ctx, cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, ctx->device));
+    CRT_CK(ctx, cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device));
+    const size_t set_aside = std::min(size_t(max_persist), size_t(want_mb * 1048576.0));
+    CRT_CK(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, set_aside));
+    cudaStreamAttrValue attr{};
+    attr.accessPolicyWindow.base_ptr = ctx->d_arena + ctx->l2_window_offset;
+    attr.accessPolicyWindow.num_bytes = std::min(ctx->l2_window_bytes, size_t(max_window));
+    double ratio = double(set_aside) / double(attr.accessPolicyWindow.num_bytes);
+    if (const char *r = std::getenv("CRT_L2_HIT"); r && *r)
+        ratio = std::atof(r);
+    attr.accessPolicyWindow.hitRatio = float(std::min(1.0, ratio));
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+    if (const char *m = std::getenv("CRT_L2_MISS"); m && *m == 's')
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    CRT_CK(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+    if (std::getenv("CRT_L2_VERBOSE"))
+        std::fprintf(stderr, "crt: L2 policy: set aside %zu MB (max %d MB), window %zu MB (max %d MB), hit ratio %.2f\n", set_aside >> 20, max_persist >> 20,
+                     size_t(attr.accessPolicyWindow.num_bytes) >> 20, max_window >> 20, attr.accessPolicyWindow.hitRatio);
+    ctx->l2_policy_on = true, ctx->l2_policy_stream = ctx->stream;
+    return CRT_OK;
+}
+
 // enqueue one frame on ctx->stream, bracketed by the timing events
 int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     if (!ctx->have_scene)
@@ -213,6 +250,8 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
     int extra_launches = 0;
     ctx->last_wavefront = false;
     ctx->last_params = *params;
+    if (int rc = apply_l2_policy(ctx))
+        return rc;
     if (stats)
         CRT_CK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(Counters), ctx->stream));
     CRT_CK(ctx, cudaEventRecord(ctx->ev_begin, ctx->stream));
@@ -550,6 +589,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // one node more than the builder made: a leaf without triangles.  A lane whose pending subtree a helper lane took
     // over finds this node in its stack instead (crt_trace_lean.cuh: lean_steal), so a visit never tests for theft
     reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset)[s->n_fast_nodes] = make_int4(0, 0, 0, 3);
+    // the device's copy of the walk tree carries its small leaves IN the child pointers (crt_walk_lean.h); the caller's
+    // crt_flat_scene keeps plain indices
+    crtwalk::inline_leaf_children(reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset), s->n_fast_nodes);
 #endif
     CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena, ctx->h_arena, total, cudaMemcpyHostToDevice, ctx->stream));
 
@@ -561,7 +603,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     std::memcpy(d.root_min, s->root_min, sizeof d.root_min);
     std::memcpy(d.root_max, s->root_max, sizeof d.root_max);
     d.n_triangles = s->n_triangles, d.n_nodes = s->n_nodes, d.n_lights = s->n_lights, d.n_materials = s->n_materials, d.n_textures = s->n_textures;
-    d.kd_empty_leaf = s->n_fast_nodes;
+    d.kd_empty_leaf = crtwalk::kInlineLeaves ? crtwalk::make_inline_leaf(0, 0) : s->n_fast_nodes;
     d.tri_verts = reinterpret_cast<const float4 *>(ctx->d_arena + parts[0].offset);
     d.tri_meta = reinterpret_cast<const int4 *>(ctx->d_arena + parts[1].offset);
     d.vert_normal = reinterpret_cast<const float4 *>(ctx->d_arena + parts[2].offset);
@@ -593,6 +635,9 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // below 20 (C4: 8 pixels per triangle).  Threshold 64; $CRT_PACKET=0|1 overrides.
     ctx->off_lights = parts[7].offset, ctx->off_materials = parts[8].offset, ctx->off_textures = parts[9].offset;
     ctx->warm_base = ctx->d_arena, ctx->warm_bytes = warm_end;
+    ctx->l2_window_offset = 0, ctx->l2_window_bytes = warm_end, ctx->l2_policy_on = false; // (a new scene: the window is set again)
+    if (const char *k = std::getenv("CRT_L2_WINDOW"); k && std::strcmp(k, "tree") == 0)
+        ctx->l2_window_offset = parts[5].offset, ctx->l2_window_bytes = warm_end - parts[5].offset;
     ctx->warm_mode = -1;
     if (const char *k = std::getenv("CRT_WARM_L2"); k && *k)
         ctx->warm_mode = (*k == '1' || *k == '2') ? 1 : 0, ctx->warm_loads = *k == '2';

@@ -75,7 +75,7 @@ __device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWal
     stolen = max(1, min(stolen, w.sp)); // entries in [1, stolen) are tombstones; popping past them frees the slots
     const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
     const bool can_give = (owns_work || helper) && !w.done() && w.node >= 0 && w.lo == 0 && w.sp - stolen >= 2 && (lowest & crtwalk::kFlagBit) == 0u &&
-                          lowest != empty_leaf;
+                          lowest != empty_leaf && !crtwalk::is_inline_leaf(int(lowest)); // (a single leaf is not worth a helper)
     const unsigned victims = __ballot_sync(full, can_give);
     if (thieves != 0u && victims != 0u) {
         const int pairs = min(__popc(thieves), __popc(victims));
@@ -118,24 +118,28 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
             break;
         const int at = w.node;
         int4 n = make_int4(0, 0, 0, 0);
-        if (!(w.tmin > threshold)) { // (a predicated load: a pruned subtree's node is never fetched)
-            n = kd_node_at(S, at);
-            if (STATS)
-                ++cn.node_tests;
-        }
+        const bool alive = !(w.tmin > threshold);
+        if (alive & !crtwalk::is_inline_leaf(at)) // (a predicated load: a pruned subtree's node is never fetched, an inline leaf has no record)
+            n = kd_node_raw(S, at);
+        if (STATS)
+            cn.node_tests += alive ? 1 : 0;
         bool took_leaf;
+        int leaf;
 #if CRT_PREFETCH_PUSH
         int pushed;
-        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, &pushed);
+        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, leaf, &pushed);
         if (pushed >= 0) // the second child will be popped later: have its record on the way (L2) by then
             asm volatile("prefetch.global.L2 [%0];" ::"l"(&S.kd_nodes[pushed]));
 #else
-        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf);
+        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, leaf);
 #endif
-        const bool park = took_leaf & (n.z > 0); // (a leaf without triangles is over at once)
-        const bool to0 = park & (parked0 < 0), to1 = park & (parked0 >= 0);
-        parked0 = to0 ? at : parked0;
-        parked1 = to1 ? at : parked1;
+        if (STATS)
+            cn.node_tests += (took_leaf && leaf != at) ? 1 : 0; // an inline leaf handed over by its parent's visit: a visit all the same
+        // (a leaf without triangles -- the tombstone of a stolen subtree -- is parked like any other: the test phase
+        //  finds nothing in it)
+        const bool to0 = took_leaf & (parked0 < 0), to1 = took_leaf & (parked0 >= 0);
+        parked0 = to0 ? leaf : parked0;
+        parked1 = to1 ? leaf : parked1;
     }
     if (!stopped)
         return false;
@@ -149,7 +153,7 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
 template <bool STATS>
 __device__ __forceinline__ void lean_test_parked(const DScene &S, LightWarpShared &ws, unsigned lane, unsigned src, int parked0, int parked1, Counters &cn) {
     const unsigned full = 0xffffffffu;
-    // the parked leaves' records again (they were loaded a few visits ago: L1)
+    // inline leaves carry {first, count} themselves; a record leaf's record again (loaded a few visits ago: L1)
     int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0;
     if (parked0 >= 0) {
         const int4 n = kd_node_at(S, parked0);

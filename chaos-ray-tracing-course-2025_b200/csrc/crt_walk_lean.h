@@ -44,6 +44,21 @@ constexpr int kDone = 0x7FFFFFFE;          // node id of the sentinel entry: the
 #endif
 constexpr int kWin = CRT_WIN;              // top-of-stack window per lane in shared memory; older entries spill
 
+// INLINE LEAVES (round 2, step 24; an experiment, OFF: measured on B200 it costs more than it saves): a
+// child pointer with kLeafTag set is not a node index but the leaf itself -- {count:4 | first reference:26} -- so a
+// walk never fetches a leaf's record: the parent's visit hands the leaf over and pops in the same iteration (9 % fewer
+// iterations, 10-12 % fewer records fetched, 13 more instructions per visit).  The upload rewrites the pointers
+// (inline_leaf_children below); leaves that do not fit (more than 15 triangles, a reference index beyond 2^26) and a
+// root that is a leaf keep their records and are recognised by axis == 3 as before.  Absent children stay -1.
+// With CRT_LEAF_INLINE=0 every term below that mentions it folds away.
+#ifndef CRT_LEAF_INLINE
+#define CRT_LEAF_INLINE 0
+#endif
+constexpr bool kInlineLeaves = CRT_LEAF_INLINE != 0;
+constexpr uint32_t kLeafTag = 0x40000000u;
+constexpr int kLeafCountShift = 26, kLeafCountMax = 15;
+constexpr uint32_t kLeafFirstMask = (1u << kLeafCountShift) - 1u;
+
 struct Node {   // crt_kd_node as the kernels load it: {split bits, a, b, axis} / {0, first, count, 3}
     int32_t x, y, z, w;
 };
@@ -69,6 +84,12 @@ CRT_WALK_FN uint32_t float_to_bits(float f) {
     return u;
 #endif
 }
+
+// id >= 0 (a node to visit or a parked leaf): is it an inline leaf?  (-1 = absent has the bit as well: ask only about ids)
+CRT_WALK_FN bool is_inline_leaf(int id) { return kInlineLeaves && (uint32_t(id) & kLeafTag) != 0u; }
+CRT_WALK_FN int inline_leaf_first(int id) { return int(uint32_t(id) & kLeafFirstMask); }
+CRT_WALK_FN int inline_leaf_count(int id) { return int((uint32_t(id) >> kLeafCountShift) & uint32_t(kLeafCountMax)); }
+CRT_WALK_FN int make_inline_leaf(int first, int count) { return int(kLeafTag | (uint32_t(count) << kLeafCountShift) | uint32_t(first)); }
 
 // pruning threshold for a best hit distance: a subtree whose interval starts beyond it cannot beat or tie the hit
 CRT_WALK_FN float prune_threshold(float best_t) { return fmaf(fabsf(best_t), 1e-5f, best_t) + 1e-6f; }
@@ -113,15 +134,18 @@ struct LeanWalker {
     // the caller has something to do first: a leaf and no room for it (leaf_room was false), or one of the two rare
     // events -- a push found the stack window full, a pop found its entry in the spill array -- which are not
     // handled here (if-converted they would cost their issue slots on every visit): call make_room(), visit again.
-    // took_leaf: `n` is a leaf, the caller takes it, the walk has moved on.
     //   threshold = prune_threshold (best_t): a subtree whose interval starts beyond it cannot beat or tie the best hit.
     //   With a wide margin and no in-plane entry pending, everything on the stack is beyond it as well (exit distances
     //   grow towards the bottom of the stack, and each interval starts where the one above it ends): the walk is over.
+    //   took_leaf: the caller takes over leaf `leaf_id` (meaningless otherwise): the id of the record leaf just visited
+    //   (`n` is its record), or an inline leaf -- the visited node itself (popped from the stack / refused before) or the
+    //   CHILD this visit would have moved to: the walk has already popped past it.
     template <class WS>
     CRT_WALK_FN bool visit(WS &ws, unsigned lane, unsigned src, const Node n, float threshold, float best_t, bool leaf_room, bool &took_leaf,
-                           int *pushed = nullptr) {
+                           int &leaf_id, int *pushed = nullptr) {
+        const int at = node;
         const bool pruned = tmin > threshold;
-        const bool leaf = n.w == 3;
+        const bool leaf = is_inline_leaf(at) | (n.w == 3); // (an inline leaf comes with n = zeros)
         const bool inner = !pruned & !leaf;
         // ---- the plane (a leaf's axis 3 reads direction.x and the word after the ray block: harmless, unused)
         const int axis = n.w;
@@ -135,14 +159,19 @@ struct LeanWalker {
         // reached" -- a slack of inf would turn both comparisons into NaN tests -- and tp = NaN means both
         const bool want_first = !(fmaf(tp, 1.00001f, 1e-6f) < tmin), want_second = !(fmaf(tp, 0.99999f, -1e-6f) > tmax);
         const bool go_first = inner & want_first & (first >= 0), go_second = inner & want_second & (second >= 0);
+        const bool to_child = go_first | go_second, both = go_first & go_second;
+        const int child = go_first ? first : second;
+        // the child is an inline leaf and the caller has room: handed over right here, and the walk pops past it (the
+        // pop below takes the entry this very visit pushes when both children are wanted)
+        const bool absorb = kInlineLeaves & to_child & is_inline_leaf(child) & leaf_room;
         // ---- rare events: nothing happens in this call
-        const bool full = go_first & go_second & (sp - lo == kWin);
+        const bool full = both & (sp - lo == kWin);
         const bool over = pruned & (flagged == 0) & (fmaf(tmin, 0.999f, -1e-4f) > best_t);
-        const bool wants_pop = (pruned & !over) | leaf | (inner & !go_first & !go_second);
-        const bool top_spilled = wants_pop & (sp - 1 < lo);
+        const bool wants_pop = (pruned & !over) | leaf | (inner & !to_child) | absorb;
+        const bool top_spilled = wants_pop & !both & (sp - 1 < lo);
         const bool frozen = full | top_spilled;
         // ---- push the second child (a predicated store), go to the first
-        const bool push = go_first & go_second & !frozen;
+        const bool push = both & !frozen;
         const bool in_plane = tp != tp;
         if (push) {
             // an in-plane entry starts at 0 instead of at the current tmax (which the NaN leaves unclipped)
@@ -154,11 +183,12 @@ struct LeanWalker {
             *pushed = push ? second : -1; // (for a prefetch of the node the walk will come back to)
         flagged += (push & in_plane) ? 1 : 0;
         tmax = push ? fminf(tmax, tp) : tmax; // NaN: unchanged
-        const bool moved = (go_first | go_second) & !frozen;
+        const bool moved = to_child & !frozen;
         tmin = (moved & !go_first) ? fmaxf(tmin, tp) : tmin; // NaN: unchanged
-        node = moved ? (go_first ? first : second) : node;
+        node = moved ? child : node;
         // ---- or hand the leaf over / pop the next pending subtree
-        const bool take_leaf = !pruned & leaf & leaf_room & !frozen, no_room = !pruned & leaf & !leaf_room;
+        const bool take_here = !pruned & leaf & leaf_room & !frozen, no_room = !pruned & leaf & !leaf_room;
+        const bool take_child = absorb & !frozen;
         const bool pop = wants_pop & !no_room & !frozen;
         sp -= pop ? 1 : 0;
         const uint32_t ex = ws.stack[sp & (kWin - 1)][lane].x, ey = ws.stack[sp & (kWin - 1)][lane].y;
@@ -168,7 +198,8 @@ struct LeanWalker {
         tmax = pop ? bits_to_float(ey) : tmax;
         node = pop ? int(ex & ~kFlagBit) : node;
         node = over ? kDone : node;
-        took_leaf = take_leaf;
+        took_leaf = take_here | take_child;
+        leaf_id = leaf ? at : child;
         return no_room | frozen;
     }
 
@@ -185,5 +216,28 @@ struct LeanWalker {
         }
     }
 };
+
+// HOST: rewrite the child pointers of a walk tree ({split, a, b, axis} / {0, first, count, 3} records with members
+// x, y, z, w) that lead to leaves small enough into inline leaves.  The leaves' records stay where they are (nothing
+// points to them any more, so they drop out of the walk's working set).  Returns how many pointers were rewritten.
+template <class NodeRec>
+inline long long inline_leaf_children(NodeRec *nodes, int n_nodes) {
+    long long rewritten = 0;
+    for (int i = 0; kInlineLeaves && i < n_nodes; ++i) {
+        if (nodes[i].w == 3)
+            continue;
+        for (int side = 0; side < 2; ++side) {
+            auto &child = side ? nodes[i].z : nodes[i].y;
+            if (child < 0 || child >= n_nodes || nodes[child].w != 3)
+                continue;
+            const long long first = nodes[child].y, count = nodes[child].z;
+            if (count < 0 || count > kLeafCountMax || first < 0 || first > (long long)kLeafFirstMask)
+                continue;
+            child = make_inline_leaf(int(first), int(count));
+            ++rewritten;
+        }
+    }
+    return rewritten;
+}
 
 } // namespace crtwalk
