@@ -589,9 +589,6 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // one node more than the builder made: a leaf without triangles.  A lane whose pending subtree a helper lane took
     // over finds this node in its stack instead (crt_trace_lean.cuh: lean_steal), so a visit never tests for theft
     reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset)[s->n_fast_nodes] = make_int4(0, 0, 0, 3);
-    // the device's copy of the walk tree carries its small leaves IN the child pointers (crt_walk_lean.h); the caller's
-    // crt_flat_scene keeps plain indices
-    crtwalk::inline_leaf_children(reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset), s->n_fast_nodes);
 #endif
     CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena, ctx->h_arena, total, cudaMemcpyHostToDevice, ctx->stream));
 
@@ -603,7 +600,7 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     std::memcpy(d.root_min, s->root_min, sizeof d.root_min);
     std::memcpy(d.root_max, s->root_max, sizeof d.root_max);
     d.n_triangles = s->n_triangles, d.n_nodes = s->n_nodes, d.n_lights = s->n_lights, d.n_materials = s->n_materials, d.n_textures = s->n_textures;
-    d.kd_empty_leaf = crtwalk::kInlineLeaves ? crtwalk::make_inline_leaf(0, 0) : s->n_fast_nodes;
+    d.kd_empty_leaf = s->n_fast_nodes;
     d.tri_verts = reinterpret_cast<const float4 *>(ctx->d_arena + parts[0].offset);
     d.tri_meta = reinterpret_cast<const int4 *>(ctx->d_arena + parts[1].offset);
     d.vert_normal = reinterpret_cast<const float4 *>(ctx->d_arena + parts[2].offset);

@@ -27,12 +27,6 @@ namespace crtdev {
 #ifndef CRT_NODE8
 #define CRT_NODE8 0
 #endif
-#if CRT_NODE8 && !defined(CRT_LEAF_INLINE)
-#define CRT_LEAF_INLINE 0 // (the packed records of that experiment have no room for inline leaves)
-#endif
-} // namespace crtdev
-#include "crt_walk_lean.h"
-namespace crtdev {
 #if CRT_NODE8
 typedef int2 KdNodeRec;
 #else
@@ -62,18 +56,7 @@ struct DScene {
     const float4 *__restrict__ texels;
 };
 
-// the record itself: for walkers that know about inline leaves (crt_walk_lean.h) and never ask for one
-__device__ __forceinline__ int4 kd_node_raw(const DScene &S, int i);
-
-// node `i` as {split, a, b, axis} / {0, first, count, 3}; an inline leaf (a child pointer that IS the leaf, see
-// crt_walk_lean.h) answers without a load
 __device__ __forceinline__ int4 kd_node_at(const DScene &S, int i) {
-    if (crtwalk::is_inline_leaf(i))
-        return make_int4(0, crtwalk::inline_leaf_first(i), crtwalk::inline_leaf_count(i), 3);
-    return kd_node_raw(S, i);
-}
-
-__device__ __forceinline__ int4 kd_node_raw(const DScene &S, int i) {
 #if CRT_NODE8
     const int2 r = __ldg(&S.kd_nodes[i]);
     const int axis = r.y & 3;

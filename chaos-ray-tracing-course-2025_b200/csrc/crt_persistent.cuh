@@ -29,7 +29,7 @@ namespace crtdev {
 #define CRT_P_PATIENCE 8
 #endif
 #ifndef CRT_P_STEPS
-#define CRT_P_STEPS 6
+#define CRT_P_STEPS 8 // (r2y: swept together with CRT_N_STEPS)
 #endif
 #ifndef CRT_P_STEPS_GI
 #define CRT_P_STEPS_GI 2 // GI queries are short (a diffuse bounce ends at the next surface): more frequent phase changes pay

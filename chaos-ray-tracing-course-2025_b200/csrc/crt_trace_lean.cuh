@@ -27,7 +27,7 @@
 namespace crtdev {
 
 #ifndef CRT_N_STEPS
-#define CRT_N_STEPS 8
+#define CRT_N_STEPS 10 // (r2y, with the 62-instruction visit of step 27: 8 -> 10 steps per round C4 2.36 -> 2.33 ms; 6: 2.43, 12: 2.35)
 #endif
 #ifndef CRT_N_TRIGGER
 #define CRT_N_TRIGGER 16
@@ -49,7 +49,7 @@ namespace crtdev {
 struct __align__(16) LightWarpShared {
     float ray[9][32];            // origin xyz, direction xyz, 1/direction xyz of each lane's ray
     unsigned long long best[32]; // (float bits of t) << 32 | triangle index
-    uint2 stack[kWin][32];       // {node | kFlagBit, entry distance bits}
+    uint2 stack[kWin][32];       // {node, exit distance bits}
     int helpers[32];             // lanes currently walking a stolen subtree of this lane's ray
 };
 
@@ -74,8 +74,8 @@ __device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWal
     const unsigned thieves = __ballot_sync(full, thief);
     stolen = max(1, min(stolen, w.sp)); // entries in [1, stolen) are tombstones; popping past them frees the slots
     const uint32_t lowest = ws.stack[stolen & (kWin - 1)][lane].x;
-    const bool can_give = (owns_work || helper) && !w.done() && w.node >= 0 && w.lo == 0 && w.sp - stolen >= 2 && (lowest & crtwalk::kFlagBit) == 0u &&
-                          lowest != empty_leaf && !crtwalk::is_inline_leaf(int(lowest)); // (a single leaf is not worth a helper)
+    const bool can_give = (owns_work || helper) && !w.done() && w.node >= 0 && w.lo == 0 && w.sp - stolen >= 2 && w.flagged == 0 &&
+                          lowest != empty_leaf;
     const unsigned victims = __ballot_sync(full, can_give);
     if (thieves != 0u && victims != 0u) {
         const int pairs = min(__popc(thieves), __popc(victims));
@@ -109,37 +109,32 @@ __device__ __forceinline__ void lean_steal(LightWarpShared &ws, crtwalk::LeanWal
 template <bool STATS, int STEPS>
 __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, crtwalk::LeanWalker &w, uint2 *spill, unsigned lane, unsigned src,
                                           int &parked0, int &parked1, Counters &cn) {
-    const float best_t = __uint_as_float(unsigned(ws.best[src] >> 32));
-    const float threshold = crtwalk::prune_threshold(best_t);
+    // where this round's visits end the walk: beyond the best hit KNOWN now (parked leaves are not tested yet)
+    const float cut = crtwalk::walk_cut(__uint_as_float(unsigned(ws.best[src] >> 32)), w.flagged);
     bool stopped = false;
 #pragma unroll
     for (int k = 0; k < STEPS; ++k) {
+        w.end_if_beyond(cut);
         if (w.done() | stopped)
             break;
         const int at = w.node;
-        int4 n = make_int4(0, 0, 0, 0);
-        const bool alive = !(w.tmin > threshold);
-        if (alive & !crtwalk::is_inline_leaf(at)) // (a predicated load: a pruned subtree's node is never fetched, an inline leaf has no record)
-            n = kd_node_raw(S, at);
+        const int4 n = kd_node_at(S, at);
         if (STATS)
-            cn.node_tests += alive ? 1 : 0;
+            ++cn.node_tests;
         bool took_leaf;
-        int leaf;
 #if CRT_PREFETCH_PUSH
         int pushed;
-        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, leaf, &pushed);
+        stopped = w.visit(ws, lane, src, as_walk_node(n), parked1 < 0, took_leaf, &pushed);
         if (pushed >= 0) // the second child will be popped later: have its record on the way (L2) by then
             asm volatile("prefetch.global.L2 [%0];" ::"l"(&S.kd_nodes[pushed]));
 #else
-        stopped = w.visit(ws, lane, src, as_walk_node(n), threshold, best_t, parked1 < 0, took_leaf, leaf);
+        stopped = w.visit(ws, lane, src, as_walk_node(n), parked1 < 0, took_leaf);
 #endif
-        if (STATS)
-            cn.node_tests += (took_leaf && leaf != at) ? 1 : 0; // an inline leaf handed over by its parent's visit: a visit all the same
         // (a leaf without triangles -- the tombstone of a stolen subtree -- is parked like any other: the test phase
         //  finds nothing in it)
         const bool to0 = took_leaf & (parked0 < 0), to1 = took_leaf & (parked0 >= 0);
-        parked0 = to0 ? leaf : parked0;
-        parked1 = to1 ? leaf : parked1;
+        parked0 = to0 ? at : parked0;
+        parked1 = to1 ? at : parked1;
     }
     if (!stopped)
         return false;
@@ -153,7 +148,7 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
 template <bool STATS>
 __device__ __forceinline__ void lean_test_parked(const DScene &S, LightWarpShared &ws, unsigned lane, unsigned src, int parked0, int parked1, Counters &cn) {
     const unsigned full = 0xffffffffu;
-    // inline leaves carry {first, count} themselves; a record leaf's record again (loaded a few visits ago: L1)
+    // the parked leaves' records again (they were loaded a few visits ago: L1)
     int p0_first = 0, p0_count = 0, p1_first = 0, p1_count = 0;
     if (parked0 >= 0) {
         const int4 n = kd_node_at(S, parked0);

@@ -19,8 +19,11 @@
 //     moment, so a pop is ONE load (before: the entry and the one below it), and a SENTINEL entry {kDone, root exit} at
 //     the bottom means pop never asks whether the stack is empty;
 //   * a ray lying IN a split plane (tp = 0 * inf = NaN) takes both children with the whole interval through the NaN
-//     semantics of the comparisons and of fminf / fmaxf; only its stack entry needs the flag bit (rare path);
-//   * pruning against the best hit is one comparison per visit against best + slack, computed once per round.
+//     semantics of the comparisons and of fminf / fmaxf; the subtree it pushes there starts where the cell starts,
+//     which an entry cannot say: the ray is FLAGGED from then on -- every pop starts at 0, no early end (a superset);
+//   * the best hit ENDS a walk, it does not prune it (step 27): before a visit the walk asks whether the subtree it
+//     stands in starts beyond best + margin (one comparison against a number computed once per round); if so,
+//     everything still on the stack does too.  The visit itself knows nothing about hits.
 // Distances carry the same slack as before (|tp| * 1e-5 + 1e-6): grazing cases visit a SUPERSET of the cells the
 // reference's six-plane box test accepts; extra leaves cannot change min (t, parse index).
 #pragma once
@@ -37,32 +40,16 @@
 
 namespace crtwalk {
 
-constexpr uint32_t kFlagBit = 0x80000000u; // stack entry pushed for a ray lying IN the split plane: its interval starts at 0
 constexpr int kDone = 0x7FFFFFFE;          // node id of the sentinel entry: the walk is over
 #ifndef CRT_WIN
 #define CRT_WIN 8
 #endif
 constexpr int kWin = CRT_WIN;              // top-of-stack window per lane in shared memory; older entries spill
 
-// INLINE LEAVES (round 2, step 24; an experiment, OFF: measured on B200 it costs more than it saves): a
-// child pointer with kLeafTag set is not a node index but the leaf itself -- {count:4 | first reference:26} -- so a
-// walk never fetches a leaf's record: the parent's visit hands the leaf over and pops in the same iteration (9 % fewer
-// iterations, 10-12 % fewer records fetched, 13 more instructions per visit).  The upload rewrites the pointers
-// (inline_leaf_children below); leaves that do not fit (more than 15 triangles, a reference index beyond 2^26) and a
-// root that is a leaf keep their records and are recognised by axis == 3 as before.  Absent children stay -1.
-// With CRT_LEAF_INLINE=0 every term below that mentions it folds away.
-#ifndef CRT_LEAF_INLINE
-#define CRT_LEAF_INLINE 0
-#endif
-constexpr bool kInlineLeaves = CRT_LEAF_INLINE != 0;
-constexpr uint32_t kLeafTag = 0x40000000u;
-constexpr int kLeafCountShift = 26, kLeafCountMax = 15;
-constexpr uint32_t kLeafFirstMask = (1u << kLeafCountShift) - 1u;
-
 struct Node {   // crt_kd_node as the kernels load it: {split bits, a, b, axis} / {0, first, count, 3}
     int32_t x, y, z, w;
 };
-struct Entry {  // {node | kFlagBit, exit distance bits}
+struct Entry {  // {node, exit distance bits}
     uint32_t x, y;
 };
 
@@ -85,26 +72,27 @@ CRT_WALK_FN uint32_t float_to_bits(float f) {
 #endif
 }
 
-// id >= 0 (a node to visit or a parked leaf): is it an inline leaf?  (-1 = absent has the bit as well: ask only about ids)
-CRT_WALK_FN bool is_inline_leaf(int id) { return kInlineLeaves && (uint32_t(id) & kLeafTag) != 0u; }
-CRT_WALK_FN int inline_leaf_first(int id) { return int(uint32_t(id) & kLeafFirstMask); }
-CRT_WALK_FN int inline_leaf_count(int id) { return int((uint32_t(id) >> kLeafCountShift) & uint32_t(kLeafCountMax)); }
-CRT_WALK_FN int make_inline_leaf(int first, int count) { return int(kLeafTag | (uint32_t(count) << kLeafCountShift) | uint32_t(first)); }
-
-// pruning threshold for a best hit distance: a subtree whose interval starts beyond it cannot beat or tie the hit
-CRT_WALK_FN float prune_threshold(float best_t) { return fmaf(fabsf(best_t), 1e-5f, best_t) + 1e-6f; }
+// Where a walk ENDS for a best hit distance: a subtree whose interval starts beyond best_t cannot beat or tie the hit,
+// and when it starts beyond it by a margin wider than the slack of the comparisons below, so does everything still on
+// the stack -- exit distances grow towards the bottom of the stack, each interval starts where the one above it ends,
+// and the walk's tmin can run ahead of those starts only by the slack a second-child move allows (1e-5 relative +
+// 1e-6; the margin is ten times that).  A FLAGGED ray (visit: it lay in a split plane at some push) has entries that
+// start earlier: no end before the stack is empty.  Computed once per round of visits.
+CRT_WALK_FN float walk_cut(float best_t, int flagged) { return flagged != 0 ? INFINITY : fmaf(best_t, 1.0001f, 1e-5f); }
 
 // WS: per-warp storage with  float ray[9][32]  (origin, direction, 1/direction)  and  Entry-like stack[kWin][32]
 // SPILL: Entry-like array of kStack entries owned by the caller (local memory on the device)
 //
-// Stack entry = {node | kFlagBit, EXIT distance of the pushed subtree}.  Its ENTRY distance need not be stored: when an
+// Stack entry = {node, EXIT distance of the pushed subtree}.  Its ENTRY distance need not be stored: when an
 // entry is popped, everything pushed after it has been popped too, so the current tmax is again what the push left
 // behind -- the plane distance the entry's interval starts at (or less, within the slack: a superset).  A pop is one
 // 8-byte load: tmin = tmax, tmax = entry.exit.
 struct LeanWalker {
     float tmin, tmax;
     int node; // node to visit next; kDone when the walk is over
-    int sp, lo, flagged;
+    int sp, lo;
+    int flagged; // 1 once this ray has pushed an entry while lying IN a split plane (see visit): from then on every popped
+                 // interval starts at 0 and the walk never ends early -- a superset, for rays that all but never occur
 
     CRT_WALK_FN bool done() const { return node == kDone; }
 
@@ -127,26 +115,23 @@ struct LeanWalker {
         ws.ray[6][lane] = ix, ws.ray[7][lane] = iy, ws.ray[8][lane] = iz;
     }
 
-    // ONE iteration of the walk of lane `src`'s ray at node `n` (= the record of `node`; anything when the subtree is
-    // pruned), written as selects: the lanes of a warp sit at unrelated nodes and must share one instruction stream
-    // (ncu r2a: the same decisions written with branches ran at 14 instead of 19 active threads per instruction and
-    // issued as many warp instructions as the walker they replaced).  Returns true when the walk could NOT move on and
-    // the caller has something to do first: a leaf and no room for it (leaf_room was false), or one of the two rare
-    // events -- a push found the stack window full, a pop found its entry in the spill array -- which are not
-    // handled here (if-converted they would cost their issue slots on every visit): call make_room(), visit again.
-    //   threshold = prune_threshold (best_t): a subtree whose interval starts beyond it cannot beat or tie the best hit.
-    //   With a wide margin and no in-plane entry pending, everything on the stack is beyond it as well (exit distances
-    //   grow towards the bottom of the stack, and each interval starts where the one above it ends): the walk is over.
-    //   took_leaf: the caller takes over leaf `leaf_id` (meaningless otherwise): the id of the record leaf just visited
-    //   (`n` is its record), or an inline leaf -- the visited node itself (popped from the stack / refused before) or the
-    //   CHILD this visit would have moved to: the walk has already popped past it.
+    // the subtree about to be visited starts beyond the cut (walk_cut): the walk is over.  Asked before every visit.
+    CRT_WALK_FN void end_if_beyond(float cut) { node = tmin > cut ? kDone : node; }
+
+    // ONE iteration of the walk of lane `src`'s ray at node `n` (= the record of `node`), written as selects: the lanes
+    // of a warp sit at unrelated nodes and must share one instruction stream (ncu r2a: the same decisions written with
+    // branches ran at 14 instead of 19 active threads per instruction and issued as many warp instructions as the walker
+    // they replaced).  Returns true when the caller has something to do before the next visit: a leaf and no room for it
+    // (leaf_room was false: nothing happened), one of the two rare events -- a push found the stack window full, a pop
+    // found its entry in the spill array: nothing happened, call make_room() and visit again; if-converted they would
+    // cost their issue slots on every visit -- or the ray has just been flagged (compute the cut again).
+    //   took_leaf: `n` is a leaf, the caller takes it, the walk has moved on.
+    // Pruning is not in here (step 27): a subtree is either visited or, beyond the cut, the end of the walk; the narrow
+    // band in between (starts beyond the best hit, but by less than the margin) is walked -- 1.5 % more visits on C4 for
+    // a dozen instructions less on every one of them.
     template <class WS>
-    CRT_WALK_FN bool visit(WS &ws, unsigned lane, unsigned src, const Node n, float threshold, float best_t, bool leaf_room, bool &took_leaf,
-                           int &leaf_id, int *pushed = nullptr) {
-        const int at = node;
-        const bool pruned = tmin > threshold;
-        const bool leaf = is_inline_leaf(at) | (n.w == 3); // (an inline leaf comes with n = zeros)
-        const bool inner = !pruned & !leaf;
+    CRT_WALK_FN bool visit(WS &ws, unsigned lane, unsigned src, const Node n, bool leaf_room, bool &took_leaf, int *pushed = nullptr) {
+        const bool leaf = n.w == 3;
         // ---- the plane (a leaf's axis 3 reads direction.x and the word after the ray block: harmless, unused)
         const int axis = n.w;
         const float split = bits_to_float(uint32_t(n.x));
@@ -158,49 +143,39 @@ struct LeanWalker {
         // that tp = -inf / +inf (direction parallel to the plane, origin off it) still means "behind" / "never
         // reached" -- a slack of inf would turn both comparisons into NaN tests -- and tp = NaN means both
         const bool want_first = !(fmaf(tp, 1.00001f, 1e-6f) < tmin), want_second = !(fmaf(tp, 0.99999f, -1e-6f) > tmax);
-        const bool go_first = inner & want_first & (first >= 0), go_second = inner & want_second & (second >= 0);
+        const bool go_first = !leaf & want_first & (first >= 0), go_second = !leaf & want_second & (second >= 0);
         const bool to_child = go_first | go_second, both = go_first & go_second;
-        const int child = go_first ? first : second;
-        // the child is an inline leaf and the caller has room: handed over right here, and the walk pops past it (the
-        // pop below takes the entry this very visit pushes when both children are wanted)
-        const bool absorb = kInlineLeaves & to_child & is_inline_leaf(child) & leaf_room;
         // ---- rare events: nothing happens in this call
         const bool full = both & (sp - lo == kWin);
-        const bool over = pruned & (flagged == 0) & (fmaf(tmin, 0.999f, -1e-4f) > best_t);
-        const bool wants_pop = (pruned & !over) | leaf | (inner & !to_child) | absorb;
-        const bool top_spilled = wants_pop & !both & (sp - 1 < lo);
+        const bool top_spilled = !to_child & (sp - 1 < lo); // (a leaf, or a node none of whose children the ray enters: pop)
         const bool frozen = full | top_spilled;
         // ---- push the second child (a predicated store), go to the first
         const bool push = both & !frozen;
-        const bool in_plane = tp != tp;
         if (push) {
-            // an in-plane entry starts at 0 instead of at the current tmax (which the NaN leaves unclipped)
-            ws.stack[sp & (kWin - 1)][lane].x = uint32_t(second) | (in_plane ? kFlagBit : 0u);
+            ws.stack[sp & (kWin - 1)][lane].x = uint32_t(second);
             ws.stack[sp & (kWin - 1)][lane].y = float_to_bits(tmax);
         }
         sp += push ? 1 : 0;
         if (pushed)
             *pushed = push ? second : -1; // (for a prefetch of the node the walk will come back to)
-        flagged += (push & in_plane) ? 1 : 0;
+        // an entry pushed in-plane starts at the current tmin, not at the tmax of the moment it is popped (which the NaN
+        // left unclipped): entries do not say where they start, so from here on EVERY pop of this ray starts at 0
+        const bool flag_now = push & (tp != tp);
+        flagged = flag_now ? 1 : flagged;
         tmax = push ? fminf(tmax, tp) : tmax; // NaN: unchanged
         const bool moved = to_child & !frozen;
         tmin = (moved & !go_first) ? fmaxf(tmin, tp) : tmin; // NaN: unchanged
-        node = moved ? child : node;
+        node = moved ? (go_first ? first : second) : node;
         // ---- or hand the leaf over / pop the next pending subtree
-        const bool take_here = !pruned & leaf & leaf_room & !frozen, no_room = !pruned & leaf & !leaf_room;
-        const bool take_child = absorb & !frozen;
-        const bool pop = wants_pop & !no_room & !frozen;
+        const bool no_room = leaf & !leaf_room;
+        const bool pop = !to_child & !no_room & !frozen;
         sp -= pop ? 1 : 0;
         const uint32_t ex = ws.stack[sp & (kWin - 1)][lane].x, ey = ws.stack[sp & (kWin - 1)][lane].y;
-        const bool flag = pop & ((ex & kFlagBit) != 0u);
-        flagged -= flag ? 1 : 0;
-        tmin = pop ? (flag ? 0.0f : tmax) : tmin;
+        tmin = pop ? (flagged != 0 ? 0.0f : tmax) : tmin;
         tmax = pop ? bits_to_float(ey) : tmax;
-        node = pop ? int(ex & ~kFlagBit) : node;
-        node = over ? kDone : node;
-        took_leaf = take_here | take_child;
-        leaf_id = leaf ? at : child;
-        return no_room | frozen;
+        node = pop ? int(ex) : node;
+        took_leaf = leaf & pop;
+        return no_room | frozen | flag_now;
     }
 
     // after visit() returned true: the oldest window entry goes to the spill array when the window is full, the top
@@ -216,28 +191,5 @@ struct LeanWalker {
         }
     }
 };
-
-// HOST: rewrite the child pointers of a walk tree ({split, a, b, axis} / {0, first, count, 3} records with members
-// x, y, z, w) that lead to leaves small enough into inline leaves.  The leaves' records stay where they are (nothing
-// points to them any more, so they drop out of the walk's working set).  Returns how many pointers were rewritten.
-template <class NodeRec>
-inline long long inline_leaf_children(NodeRec *nodes, int n_nodes) {
-    long long rewritten = 0;
-    for (int i = 0; kInlineLeaves && i < n_nodes; ++i) {
-        if (nodes[i].w == 3)
-            continue;
-        for (int side = 0; side < 2; ++side) {
-            auto &child = side ? nodes[i].z : nodes[i].y;
-            if (child < 0 || child >= n_nodes || nodes[child].w != 3)
-                continue;
-            const long long first = nodes[child].y, count = nodes[child].z;
-            if (count < 0 || count > kLeafCountMax || first < 0 || first > (long long)kLeafFirstMask)
-                continue;
-            child = make_inline_leaf(int(first), int(count));
-            ++rewritten;
-        }
-    }
-    return rewritten;
-}
 
 } // namespace crtwalk

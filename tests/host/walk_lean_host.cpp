@@ -98,14 +98,6 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
     if (!s || !rays || !s->fast_nodes)
         return -1;
     std::vector<Entry> spill(64);
-    // the walk tree as the device holds it: small leaves inline in the child pointers (crt_cuda_upload_scene does the same)
-    std::vector<Node> nodes(size_t(s->n_fast_nodes));
-    for (int i = 0; i < s->n_fast_nodes; ++i) {
-        const crt_kd_node &k = s->fast_nodes[i];
-        std::memcpy(&nodes[size_t(i)].x, &k.split, 4);
-        nodes[size_t(i)].y = k.a, nodes[size_t(i)].z = k.b, nodes[size_t(i)].w = k.axis;
-    }
-    crtwalk::inline_leaf_children(nodes.data(), s->n_fast_nodes);
     for (int r = 0; r < n; ++r) {
         const V o{ rays[6 * r], rays[6 * r + 1], rays[6 * r + 2] }, d{ rays[6 * r + 3], rays[6 * r + 4], rays[6 * r + 5] };
         V inv;
@@ -116,41 +108,33 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
             HostWarp ws{};
             LeanWalker w;
             w.start(ws, 0u, o.x, o.y, o.z, d.x, d.y, d.z, inv.x, inv.y, inv.z, t_enter, t_exit);
-            float seen_t = best.t; // the distance the pruning uses
+            float seen_t = best.t; // the distance the walk's end is decided with
             int pending = 0;
             bool refuse_next = false;
-            long long steps = 0;
-            while (!w.done()) {
+            for (;;) {
+                // the device computes the cut once per round of visits: here a round is one visit
+                w.end_if_beyond(crtwalk::walk_cut(seen_t, w.flagged));
+                if (w.done())
+                    break;
                 if (w.sp - w.lo > crtwalk::kWin || w.sp > 60)
                     return -2; // stack discipline broken
-                const float threshold = crtwalk::prune_threshold(seen_t);
-                Node node{ 0, 0, 0, 0 };
-                const int at = w.node;
-                const bool alive = !(w.tmin > threshold);
-                if (alive && !crtwalk::is_inline_leaf(at)) {
-                    if (at < 0 || at >= s->n_fast_nodes)
-                        return -4; // the walk asked for a record that does not exist
-                    node = nodes[size_t(at)];
-                    ++visits;
-                }
+                if (w.node < 0 || w.node >= s->n_fast_nodes)
+                    return -4; // the walk asked for a record that does not exist
+                const crt_kd_node &k = s->fast_nodes[w.node];
+                Node node;
+                std::memcpy(&node.x, &k.split, 4);
+                node.y = k.a, node.z = k.b, node.w = k.axis;
+                ++visits;
                 // every other leaf is refused once (no room) and must be offered again: the device's blocked lanes
-                const bool room = !refuse_next;
-                const bool leaf_here = crtwalk::is_inline_leaf(at) || node.w == 3;
-                int leaf = -1;
+                const bool room = !(refuse_next && node.w == 3);
                 bool took_leaf = false;
-                const bool stopped = w.visit(ws, 0u, 0u, node, threshold, seen_t, room, took_leaf, leaf);
-                if (stopped && leaf_here && !room && alive)
+                const bool stopped = w.visit(ws, 0u, 0u, node, room, took_leaf);
+                if (stopped && node.w == 3 && !room)
                     refuse_next = false; // refused once: the next offer of this leaf is taken
                 if (took_leaf) {
-                    if (leaf < 0)
-                        return -6;
                     refuse_next = true;
-                    const int first = crtwalk::is_inline_leaf(leaf) ? crtwalk::inline_leaf_first(leaf) : node.y;
-                    const int count = crtwalk::is_inline_leaf(leaf) ? crtwalk::inline_leaf_count(leaf) : node.z;
-                    if (!crtwalk::is_inline_leaf(leaf) && leaf != at)
-                        return -5; // a record leaf can only be the visited node
-                    for (int i = 0; i < count; ++i) {
-                        const uint32_t ref = s->fast_refs[first + i];
+                    for (int i = 0; i < node.z; ++i) {
+                        const uint32_t ref = s->fast_refs[node.y + i];
                         float t;
                         if (triangle_test(*s, ref, o, d, t))
                             best.offer(t, int(ref & 0x7FFFFFFFu));
@@ -163,7 +147,7 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
                     w.make_room(ws, spill.data(), 0u);
                     *rare_events += w.lo != lo_before;
                 }
-                if (++steps > 50000000)
+                if (visits > 50000000)
                     return -3; // runaway walk
             }
         }

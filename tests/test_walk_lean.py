@@ -28,17 +28,6 @@ def host():
     return C.CDLL(LIB)
 
 
-@pytest.fixture(scope="module")
-def host_inline():
-    """the same walker built WITH inline leaves (-DCRT_LEAF_INLINE=1, an experiment that is off in the shipped build)"""
-    lib = LIB.replace(".so", "_inline.so")
-    if not os.path.exists(lib) or os.path.getmtime(lib) < max(os.path.getmtime(SRC), os.path.getmtime(HEADER)):
-        os.makedirs(os.path.dirname(lib), exist_ok=True)
-        subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-fno-fast-math", "-DCRT_LEAF_INLINE=1",
-                        "-I" + os.path.join(ROOT, "include"), SRC, "-o", lib], check=True)
-    return C.CDLL(lib)
-
-
 def closest(host, flat, rays, lazy=0, brute=False):
     rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
     n = len(rays)
@@ -153,16 +142,3 @@ def test_lean_walk_work_is_bounded(crt, ot, host):
     _, _, visits = closest(host, flat, rays)
     assert visits.mean() < 40 and visits.max() < 2000, (visits.mean(), visits.max())
 
-
-@pytest.mark.parametrize("rel", ["14-01-acceleration-tree/scene1.crtscene", "15-01-conclusion/scene2.crtscene"])
-def test_inline_leaves_change_the_fetches_not_the_winners(crt, ot, host, host_inline, rel):
-    """small leaves live in their parent's child pointer (crt_walk_lean.h: inline_leaf_children): the walk hands them
-    over from the parent's visit and never loads their record -- same closest hits, clearly fewer node records"""
-    flat = crt.Scene.load_json(ot.scene_variant(rel, 160, 90), os.path.dirname(ot.scene_file(rel))).flatten(reference_tree=False)
-    rays = ray_set(flat, ot, np.random.default_rng(5))
-    for lazy in (0, 2):
-        tri_a, t_a, visits_a = closest(host_inline, flat, rays, lazy=lazy)
-        tri_b, t_b, visits_b = closest(host, flat, rays, lazy=lazy)
-        assert np.array_equal(tri_a, tri_b) and np.array_equal(otools.bits(t_a), otools.bits(t_b))
-        assert (visits_a <= visits_b).all()
-        assert visits_a.sum() < 0.95 * visits_b.sum(), (visits_a.sum(), visits_b.sum())

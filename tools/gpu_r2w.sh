@@ -16,8 +16,8 @@ for rep in 1 2; do
     lib=$V/libcrt_b200_$v.so; [ $v = default ] && lib=$PWD/chaos-ray-tracing-course-2025_b200/lib/libcrt_b200.so
     t "$v c4" CRT_B200_LIB=$lib timeout 200 python tools/render_frames.py c4 6 auto kd 0
     t "$v c4 rank0of8" CRT_B200_LIB=$lib CRT_RANK=0 CRT_WORLD=8 timeout 200 python tools/render_frames.py c4 6 auto kd 0
-    t "$v c5" CRT_B200_LIB=$lib timeout 200 python tools/render_frames.py c5 6 auto kd 0
-    t "$v c3" CRT_B200_LIB=$lib timeout 200 python tools/render_frames.py c3 6 auto kd 0
+    [ $rep = 1 ] && t "$v c5" CRT_B200_LIB=$lib timeout 200 python tools/render_frames.py c5 6 auto kd 0
+    [ $rep = 1 ] && t "$v c3" CRT_B200_LIB=$lib timeout 200 python tools/render_frames.py c3 6 auto kd 0
     [ $rep = 1 ] && t "$v c3-gi" CRT_B200_LIB=$lib timeout 300 python tools/render_frames.py c3-gi 2 auto kd 0
   done
 done
