@@ -589,6 +589,12 @@ int crt_cuda_upload_scene(crt_cuda_ctx *ctx, const crt_flat_scene *s) {
     // one node more than the builder made: a leaf without triangles.  A lane whose pending subtree a helper lane took
     // over finds this node in its stack instead (crt_trace_lean.cuh: lean_steal), so a visit never tests for theft
     reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset)[s->n_fast_nodes] = make_int4(0, 0, 0, 3);
+    if (crtwalk::kLeafNeg) { // the device's leaves: {0, ~first, ~count, 3} (crt_walk_lean.h); the caller's crt_flat_scene stays plain
+        int4 *recs = reinterpret_cast<int4 *>(ctx->h_arena + parts[5].offset);
+        for (int i = 0; i <= s->n_fast_nodes; ++i)
+            if (recs[i].w == 3)
+                recs[i].y = ~recs[i].y, recs[i].z = ~recs[i].z;
+    }
 #endif
     CRT_CK(ctx, cudaMemcpyAsync(ctx->d_arena, ctx->h_arena, total, cudaMemcpyHostToDevice, ctx->stream));
 

@@ -27,6 +27,12 @@ namespace crtdev {
 #ifndef CRT_NODE8
 #define CRT_NODE8 0
 #endif
+#if CRT_NODE8 && !defined(CRT_LEAF_NEG)
+#define CRT_LEAF_NEG 0 // (the packed records of that experiment keep their own leaf form)
+#endif
+} // namespace crtdev
+#include "crt_walk_lean.h"
+namespace crtdev {
 #if CRT_NODE8
 typedef int2 KdNodeRec;
 #else
@@ -56,7 +62,18 @@ struct DScene {
     const float4 *__restrict__ texels;
 };
 
+// the record as the device holds it (crt_walk_lean.h, CRT_LEAF_NEG: a leaf is {0, ~first, ~count, 3})
+__device__ __forceinline__ int4 kd_node_raw(const DScene &S, int i);
+
+// node `i` as {split, a, b, axis} / {0, first, count, 3}
 __device__ __forceinline__ int4 kd_node_at(const DScene &S, int i) {
+    int4 n = kd_node_raw(S, i);
+    if (crtwalk::kLeafNeg && n.w == 3)
+        n.y = ~n.y, n.z = ~n.z;
+    return n;
+}
+
+__device__ __forceinline__ int4 kd_node_raw(const DScene &S, int i) {
 #if CRT_NODE8
     const int2 r = __ldg(&S.kd_nodes[i]);
     const int axis = r.y & 3;

@@ -41,6 +41,9 @@ namespace crtdev {
 #ifndef CRT_N_REFILL
 #define CRT_N_REFILL 25
 #endif
+#ifndef CRT_PARK_SHIFT
+#define CRT_PARK_SHIFT 1 // (two selects under one predicate instead of two predicates: 62 -> 60 instructions per visit)
+#endif
 #ifndef CRT_PREFETCH_PUSH
 #define CRT_PREFETCH_PUSH 0
 #endif
@@ -114,11 +117,12 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
     bool stopped = false;
 #pragma unroll
     for (int k = 0; k < STEPS; ++k) {
-        w.end_if_beyond(cut);
-        if (w.done() | stopped)
+        // (beyond the cut the walk is over: the lane leaves the round here and is marked after it -- a lane that leaves
+        //  because it is stopped stands where its last check found it within the cut)
+        if ((w.tmin > cut) | w.done() | stopped)
             break;
         const int at = w.node;
-        const int4 n = kd_node_at(S, at);
+        const int4 n = kd_node_raw(S, at);
         if (STATS)
             ++cn.node_tests;
         bool took_leaf;
@@ -132,10 +136,16 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
 #endif
         // (a leaf without triangles -- the tombstone of a stolen subtree -- is parked like any other: the test phase
         //  finds nothing in it)
+#if CRT_PARK_SHIFT
+        parked1 = took_leaf ? parked0 : parked1; // (the newest leaf in slot 0, the one before it moves to slot 1)
+        parked0 = took_leaf ? at : parked0;
+#else
         const bool to0 = took_leaf & (parked0 < 0), to1 = took_leaf & (parked0 >= 0);
         parked0 = to0 ? at : parked0;
         parked1 = to1 ? at : parked1;
+#endif
     }
+    w.end_if_beyond(cut);
     if (!stopped)
         return false;
     w.make_room(ws, spill, lane); // (rare: stack window full / popped entry spilled; nothing to do for a blocked leaf)

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
         }
         // a ray that misses the root box hits nothing: its pixel is final here; the others are queued for the level-0
         // shade (slot only -- the shade stage regenerates the camera ray, as it does after k_wf_raygen)
-        if (have && !q.live)
+        if (__any_sync(full, have && !q.live) && !write_patch_background(S, P, b, patch, lane, rgb, rgb8) && have && !q.live)
             write_pixel(S, rgb, rgb8, x, ly, mk(S.bg[0], S.bg[1], S.bg[2]));
         const unsigned live_mask = __ballot_sync(full, q.live);
         if (live_mask == 0u)
@@ -77,12 +77,13 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
             const bool act = tmax != kOut && !(tmin - (fabsf(tmin) * 1e-5f + 1e-6f) > best_t);
             bool descend = false;
             if (__any_sync(full, act)) {
-                const int4 n = kd_node_at(S, node);
+                const int4 n = kd_node_raw(S, node); // (a leaf's {first, count} are stored complemented: crt_walk_lean.h, CRT_LEAF_NEG)
                 if (STATS && act && node != 0)
                     ++cn.node_tests;
                 if (n.w == 3) {
-                    for (int k = 0; k < n.z; ++k) {
-                        const uint32_t ref = __ldg(&S.kd_refs[n.y + k]);
+                    const int leaf_first = crtwalk::kLeafNeg ? ~n.y : n.y, leaf_count = crtwalk::kLeafNeg ? ~n.z : n.z;
+                    for (int k = 0; k < leaf_count; ++k) {
+                        const uint32_t ref = __ldg(&S.kd_refs[leaf_first + k]);
                         const int tri = int(ref & 0x7FFFFFFFu);
                         const float4 A = __ldg(&S.tri_verts[3 * tri]), B = __ldg(&S.tri_verts[3 * tri + 1]), C = __ldg(&S.tri_verts[3 * tri + 2]);
                         if (act) {

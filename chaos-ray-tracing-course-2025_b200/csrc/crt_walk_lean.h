@@ -46,7 +46,15 @@ constexpr int kDone = 0x7FFFFFFE;          // node id of the sentinel entry: the
 #endif
 constexpr int kWin = CRT_WIN;              // top-of-stack window per lane in shared memory; older entries spill
 
-struct Node {   // crt_kd_node as the kernels load it: {split bits, a, b, axis} / {0, first, count, 3}
+// CRT_LEAF_NEG: the device's copy of a LEAF record is {0, ~first, ~count, 3}: both "children" of a leaf are negative =
+// absent, so the visit needs no "and not a leaf" on its two child decisions (crt_cuda_upload_scene rewrites the records,
+// kd_node_at hands the plain form to the kernels that do not use this walker)
+#ifndef CRT_LEAF_NEG
+#define CRT_LEAF_NEG 1
+#endif
+constexpr bool kLeafNeg = CRT_LEAF_NEG != 0;
+
+struct Node {   // crt_kd_node as the kernels load it: {split bits, a, b, axis} / {0, first, count, 3} (see CRT_LEAF_NEG)
     int32_t x, y, z, w;
 };
 struct Entry {  // {node, exit distance bits}
@@ -143,7 +151,8 @@ struct LeanWalker {
         // that tp = -inf / +inf (direction parallel to the plane, origin off it) still means "behind" / "never
         // reached" -- a slack of inf would turn both comparisons into NaN tests -- and tp = NaN means both
         const bool want_first = !(fmaf(tp, 1.00001f, 1e-6f) < tmin), want_second = !(fmaf(tp, 0.99999f, -1e-6f) > tmax);
-        const bool go_first = !leaf & want_first & (first >= 0), go_second = !leaf & want_second & (second >= 0);
+        const bool inner = kLeafNeg | !leaf; // (kLeafNeg: a leaf's "children" are negative)
+        const bool go_first = inner & want_first & (first >= 0), go_second = inner & want_second & (second >= 0);
         const bool to_child = go_first | go_second, both = go_first & go_second;
         // ---- rare events: nothing happens in this call
         const bool full = both & (sp - lo == kWin);

@@ -124,6 +124,9 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
                 Node node;
                 std::memcpy(&node.x, &k.split, 4);
                 node.y = k.a, node.z = k.b, node.w = k.axis;
+                const int leaf_first = k.a, leaf_count = k.b;
+                if (crtwalk::kLeafNeg && node.w == 3)
+                    node.y = ~node.y, node.z = ~node.z; // as crt_cuda_upload_scene stores leaves on the device
                 ++visits;
                 // every other leaf is refused once (no room) and must be offered again: the device's blocked lanes
                 const bool room = !(refuse_next && node.w == 3);
@@ -133,8 +136,8 @@ int walk_lean_closest(const crt_flat_scene *s, const float *rays, int n, int laz
                     refuse_next = false; // refused once: the next offer of this leaf is taken
                 if (took_leaf) {
                     refuse_next = true;
-                    for (int i = 0; i < node.z; ++i) {
-                        const uint32_t ref = s->fast_refs[node.y + i];
+                    for (int i = 0; i < leaf_count; ++i) {
+                        const uint32_t ref = s->fast_refs[leaf_first + i];
                         float t;
                         if (triangle_test(*s, ref, o, d, t))
                             best.offer(t, int(ref & 0x7FFFFFFFu));
