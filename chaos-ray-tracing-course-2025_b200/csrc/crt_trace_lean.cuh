@@ -129,8 +129,13 @@ __device__ __forceinline__ bool lean_walk(const DScene &S, LightWarpShared &ws, 
 #if CRT_PREFETCH_PUSH
         int pushed;
         stopped = w.visit(ws, lane, src, as_walk_node(n), parked1 < 0, took_leaf, &pushed);
-        if (pushed >= 0) // the second child will be popped later: have its record on the way (L2) by then
+        if (pushed >= 0) { // the walk will come back to this node: have its record on the way by then (1: to L2; 2: to L1 -- r3b: neither pays, 2.36-2.41 against 2.32-2.37 ms)
+#if CRT_PREFETCH_PUSH >= 2
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(&S.kd_nodes[pushed]));
+#else
             asm volatile("prefetch.global.L2 [%0];" ::"l"(&S.kd_nodes[pushed]));
+#endif
+        }
 #else
         stopped = w.visit(ws, lane, src, as_walk_node(n), parked1 < 0, took_leaf);
 #endif

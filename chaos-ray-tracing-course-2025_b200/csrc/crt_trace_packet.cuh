@@ -19,7 +19,7 @@
 namespace crtdev {
 
 #ifndef CRT_K_MINBLOCKS
-#define CRT_K_MINBLOCKS 8
+#define CRT_K_MINBLOCKS 10 // (48 registers: ten blocks per SM; with 8 the compiler settles at 52 = nine blocks and C1 / C3 lose 3-6 %)
 #endif
 
 template <bool STATS>
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(kTraceBlock, CRT_K_MINBLOCKS) k_wf_trace_packe
         }
         // a ray that misses the root box hits nothing: its pixel is final here; the others are queued for the level-0
         // shade (slot only -- the shade stage regenerates the camera ray, as it does after k_wf_raygen)
-        if (__any_sync(full, have && !q.live) && !write_patch_background(S, P, b, patch, lane, rgb, rgb8) && have && !q.live)
+        if (have && !q.live)
             write_pixel(S, rgb, rgb8, x, ly, mk(S.bg[0], S.bg[1], S.bg[2]));
         const unsigned live_mask = __ballot_sync(full, q.live);
         if (live_mask == 0u)

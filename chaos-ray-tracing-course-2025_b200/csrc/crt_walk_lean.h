@@ -165,8 +165,6 @@ struct LeanWalker {
             ws.stack[sp & (kWin - 1)][lane].y = float_to_bits(tmax);
         }
         sp += push ? 1 : 0;
-        if (pushed)
-            *pushed = push ? second : -1; // (for a prefetch of the node the walk will come back to)
         // an entry pushed in-plane starts at the current tmin, not at the tmax of the moment it is popped (which the NaN
         // left unclipped): entries do not say where they start, so from here on EVERY pop of this ray starts at 0
         const bool flag_now = push & (tp != tp);
@@ -184,6 +182,8 @@ struct LeanWalker {
         tmax = pop ? bits_to_float(ey) : tmax;
         node = pop ? int(ex) : node;
         took_leaf = leaf & pop;
+        if (pushed)
+            *pushed = push ? second : -1; // (experiment CRT_PREFETCH_PUSH: a prefetch of the node the walk will come back to)
         return no_room | frozen | flag_now;
     }
 

@@ -109,33 +109,6 @@ constexpr int kRaygenBlock = 256;
 
 __device__ __forceinline__ void write_pixel(const DScene &S, float *__restrict__ rgb, uint8_t *__restrict__ rgb8, int x, int ly, V3 c);
 
-// The background colour for a whole 8x4 patch (one warp), when the patch lies wholly inside the frame: every pixel of it
-// whose ray does enter the root box is written again by the level-0 shade or resolve, so the patch can be filled as a
-// whole, in 16-byte and 8-byte vectors -- 24 + 12 store lanes per warp instead of six scalar stores per lane, each of
-// which fills a third of the sectors it touches.  false: not done (ragged patch / odd width), write pixel by pixel.
-__device__ __forceinline__ bool write_patch_background(const DScene &S, const DParams &P, const WfBuffers &b, int patch, unsigned lane,
-                                                       float *__restrict__ rgb, uint8_t *__restrict__ rgb8) {
-    const int x0 = (patch % b.patches_x) * 8, ly0 = (patch / b.patches_x) * 4;
-    const bool whole = !P.coherent && (S.cam.width & 7) == 0 && x0 + 8 <= S.cam.width && ly0 + 4 <= P.rows &&
-                       (reinterpret_cast<uintptr_t>(rgb) & 15u) == 0 && (reinterpret_cast<uintptr_t>(rgb8) & 7u) == 0;
-    if (!whole)
-        return false;
-    const float cr = S.bg[0], cg = S.bg[1], cb = S.bg[2];
-    if (rgb && lane < 24u) {
-        const int row = int(lane) / 6, j = int(lane) % 6, m = j % 3; // the rgb stream of a row, four floats at a time
-        const float4 v = m == 0 ? make_float4(cr, cg, cb, cr) : (m == 1 ? make_float4(cg, cb, cr, cg) : make_float4(cb, cr, cg, cb));
-        put_stream(reinterpret_cast<float4 *>(rgb + (size_t(ly0 + row) * S.cam.width + x0) * 3) + j, v);
-    }
-    if (rgb8 && lane < 12u) {
-        const int row = int(lane) / 3, j = int(lane) % 3; // ... and eight bytes at a time
-        const unsigned r8 = quantize(cr), g8 = quantize(cg), b8 = quantize(cb);
-        const unsigned c0 = j == 0 ? r8 : (j == 1 ? b8 : g8), c1 = j == 0 ? g8 : (j == 1 ? r8 : b8), c2 = j == 0 ? b8 : (j == 1 ? g8 : r8);
-        put_stream(reinterpret_cast<uint2 *>(rgb8 + (size_t(ly0 + row) * S.cam.width + x0) * 3) + j,
-                   make_uint2(c0 | (c1 << 8) | (c2 << 16) | (c0 << 24), c1 | (c2 << 8) | (c0 << 16) | (c1 << 24)));
-    }
-    return true;
-}
-
 template <bool STATS>
 __global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constant__ DScene S, const __grid_constant__ DParams P,
                                                              const __grid_constant__ WfBuffers b, Counters *__restrict__ counters,
@@ -178,8 +151,7 @@ __global__ void __launch_bounds__(kRaygenBlock) k_wf_raygen(const __grid_constan
         }
         // a ray that misses the root box hits nothing (crt_renderer.cpp:142-144): its pixel is final here, and the
         // level-0 shade only visits the queued rays
-        const bool miss = have && !q.live;
-        if (__any_sync(0xffffffffu, miss) && !write_patch_background(S, P, b, first >> 5, lane, rgb, rgb8) && miss)
+        if (have && !q.live)
             write_pixel(S, rgb, rgb8, x, ly, mk(S.bg[0], S.bg[1], S.bg[2]));
     }
     if (STATS)
