@@ -19,9 +19,10 @@ struct KdBuildStats {
 struct KdBuildParams {
     float c_node{ 1.0f };  // cost of one node step of the trace kernel (the unit)
     float c_leaf{ 1.0f };  // fixed cost of parking a leaf for the next test phase
-    float c_tri{ 1.0f };   // cost per tested triangle.  Swept on B200 again with the lean kernels (tools/gpu_sah.sh,
-                           // profiles/r2p_*): node visits are what the latency-bound walk pays for, tests run warp-wide --
-                           // 1.5 -> 1.0: C4 2.82 -> 2.77 ms, one rank's share of an 8-rank frame 0.88 -> 0.80 ms, GI 156.4 -> 154.8 ms
+    float c_tri{ 0.75f };  // cost per tested triangle.  Swept on B200 with every generation of the kernels (tools/gpu_sah.sh,
+                           // profiles/r2p_*, r3g_*): node visits are what the walk pays for, tests run warp-wide --
+                           // 1.5 -> 1.0 (r2p): C4 2.82 -> 2.77 ms, GI 156.4 -> 154.8 ms; 1.0 -> 0.7 .. 0.85 with the
+                           // 58-instruction visit (r3g, three interleaved passes): 2.276 -> 2.256 ms; 0.6: 2.276
     float empty_bonus{ 1.0f }; // < 1 favours splits that cut away empty space; the sweep on B200 found no gain from it
     int max_depth{ 44 };   // device stack: fast_max_depth + 2 <= kStack (48)
     int exact_below{ 96 }; // nodes with at most this many triangles sweep every triangle bound; larger ones use bins

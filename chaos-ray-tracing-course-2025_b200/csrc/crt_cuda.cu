@@ -321,7 +321,7 @@ int enqueue_frame(crt_cuda_ctx *ctx, const crt_render_params *params) {
             int launches = 0;
             const bool deeper = ctx->has_secondary && dp.max_ray_depth > 0;
             // levels 0 .. seed-1 as wavefront kernels; $CRT_HYBRID_LEVEL moves the hand-over
-            int seed = dp.max_ray_depth >= 5 && params->world <= 1 ? 2 : 1; // C4: 3.09 ms with 1, 3.01 ms with 2
+            int seed = 1; // (round 1: C4 3.09 ms with 1, 3.01 ms with 2; with the lean visit of round 2, r3c: 2.25 with 1, 2.31 with 2, 2.39 with 3)
             if (const char *v = std::getenv("CRT_HYBRID_LEVEL"); v && *v)
                 seed = std::max(1, std::atoi(v));
             seed = deeper ? std::min(seed, int(dp.max_ray_depth)) : 1;

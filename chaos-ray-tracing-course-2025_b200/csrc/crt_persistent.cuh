@@ -29,7 +29,7 @@ namespace crtdev {
 #define CRT_P_PATIENCE 8
 #endif
 #ifndef CRT_P_STEPS
-#define CRT_P_STEPS 8 // (r2y: swept together with CRT_N_STEPS)
+#define CRT_P_STEPS 10 // (r2y: swept together with CRT_N_STEPS; r3g, with levels 1-8 of C4 in this kernel: 6 / 8 / 10 / 12 -> 2.29 / 2.27 / 2.25 / 2.28 ms)
 #endif
 #ifndef CRT_P_STEPS_GI
 #define CRT_P_STEPS_GI 2 // GI queries are short (a diffuse bounce ends at the next surface): more frequent phase changes pay
