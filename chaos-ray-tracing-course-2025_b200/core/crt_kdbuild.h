@@ -19,10 +19,11 @@ struct KdBuildStats {
 struct KdBuildParams {
     float c_node{ 1.0f };  // cost of one node step of the trace kernel (the unit)
     float c_leaf{ 1.0f };  // fixed cost of parking a leaf for the next test phase
-    float c_tri{ 0.75f };  // cost per tested triangle.  Swept on B200 with every generation of the kernels (tools/gpu_sah.sh,
-                           // profiles/r2p_*, r3g_*): node visits are what the walk pays for, tests run warp-wide --
-                           // 1.5 -> 1.0 (r2p): C4 2.82 -> 2.77 ms, GI 156.4 -> 154.8 ms; 1.0 -> 0.7 .. 0.85 with the
-                           // 58-instruction visit (r3g, three interleaved passes): 2.276 -> 2.256 ms; 0.6: 2.276
+    float c_tri{ 1.0f };   // cost per tested triangle.  Swept on B200 with every generation of the kernels (tools/gpu_sah.sh,
+                           // profiles/r2p_*, r3g_*, r3h_*): node visits are what the walk pays for, tests run warp-wide --
+                           // 1.5 -> 1.0 (r2p): C4 2.82 -> 2.77 ms, GI 156.4 -> 154.8 ms.  0.75 with the 58-instruction
+                           // visit: C4 -1 % (r3g), but C3 0.61 -> 0.71 ms and C5 0.31 -> 0.35 ms (r3h): the packet kernel of
+                           // the primary level tests a leaf's triangles one after the other -- stays 1.0
     float empty_bonus{ 1.0f }; // < 1 favours splits that cut away empty space; the sweep on B200 found no gain from it
     int max_depth{ 44 };   // device stack: fast_max_depth + 2 <= kStack (48)
     int exact_below{ 96 }; // nodes with at most this many triangles sweep every triangle bound; larger ones use bins
