@@ -40,6 +40,10 @@ namespace crtdev {
 #ifndef CRT_P_SHADE_TRIGGER
 #define CRT_P_SHADE_TRIGGER 12
 #endif
+#ifndef CRT_P_EAGER_MISS
+#define CRT_P_EAGER_MISS 0 // 1: queries without a hit and freshly taken work items continue at once, hits wait for the batch (step 29:
+                           // parity-green, measured, slower -- C4 2.27 -> 2.30 ms, one rank's share of an 8-rank frame 0.66 -> 0.70 ms)
+#endif
 #ifndef CRT_P_FAST_UNWIND
 #define CRT_P_FAST_UNWIND 1 // return path of reflection chains: the frames' loads four at a time (step 25)
 #endif
@@ -178,14 +182,21 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         __syncwarp();
         // ---- SHADE phase: lanes whose query is finished (or whose pixel is new) continue their pixel's recursion
         const bool ready = ply >= 0 && w.done() && parked0 < 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
-        const unsigned ready_m = __ballot_sync(full, ready);
+        // (experiment, off -- step 29.)  What a lane waits for a well-filled phase with is the LONG continuation: surface,
+        // material, the next ray.  A query that hit nothing only returns the background colour through its frames, and a
+        // work item just taken only needs its ray set up: with CRT_P_EAGER_MISS those go at once and the batch holds hits
+        // only.  Measured slower: the short phases interrupt the walking lanes more often than the freed lanes help.
+        const bool at_once = CRT_P_EAGER_MISS && !GI && ready && !(SHADOWS && shadow_q) &&
+                             (fresh || !live || unsigned(ws.best[lane] & 0xffffffffull) == 0xffffffffu);
+        const unsigned ready_m = __ballot_sync(full, ready && !at_once);
         const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && !w.done());
         patience = ready_m != 0u ? patience + 1 : 0;
         // (with the queue empty a ready lane continues at once: its pixel's remaining bounces are the critical path)
-        if (ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u ||
-                              patience >= (exhausted && !GI ? 1 : (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE)))) {
-            patience = 0;
-            if (ready) {
+        const bool batch = ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u ||
+                                             patience >= (exhausted && !GI ? 1 : (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE)));
+        if (batch || __any_sync(full, at_once)) {
+            patience = batch ? 0 : patience;
+            if (ready && (batch || at_once)) {
                 int act = 0; // 0: consume the finished query, 1: shade_ray(ray, depth) entry, 2: return c to the callers
                 Ray ray{};
                 V3 c = mk(0.0f, 0.0f, 0.0f);
