@@ -182,19 +182,24 @@ __global__ void __launch_bounds__(kTraceBlock, GI ? CRT_P_MINBLOCKS_GI : CRT_P_M
         __syncwarp();
         // ---- SHADE phase: lanes whose query is finished (or whose pixel is new) continue their pixel's recursion
         const bool ready = ply >= 0 && w.done() && parked0 < 0 && (!live || *(volatile int *)&ws.helpers[lane] == 0);
+#if CRT_P_EAGER_MISS
         // (experiment, off -- step 29.)  What a lane waits for a well-filled phase with is the LONG continuation: surface,
         // material, the next ray.  A query that hit nothing only returns the background colour through its frames, and a
-        // work item just taken only needs its ray set up: with CRT_P_EAGER_MISS those go at once and the batch holds hits
-        // only.  Measured slower: the short phases interrupt the walking lanes more often than the freed lanes help.
-        const bool at_once = CRT_P_EAGER_MISS && !GI && ready && !(SHADOWS && shadow_q) &&
-                             (fresh || !live || unsigned(ws.best[lane] & 0xffffffffull) == 0xffffffffu);
+        // work item just taken only needs its ray set up: here those go at once and the batch holds hits only.  Measured
+        // slower: the short phases interrupt the walking lanes more often than the freed lanes help.
+        const bool at_once = !GI && ready && !(SHADOWS && shadow_q) && (fresh || !live || unsigned(ws.best[lane] & 0xffffffffull) == 0xffffffffu);
         const unsigned ready_m = __ballot_sync(full, ready && !at_once);
+        const bool any_at_once = __any_sync(full, at_once);
+#else
+        const bool at_once = false, any_at_once = false;
+        const unsigned ready_m = __ballot_sync(full, ready);
+#endif
         const unsigned walking_m = __ballot_sync(full, (ply >= 0 || helper) && !w.done());
         patience = ready_m != 0u ? patience + 1 : 0;
         // (with the queue empty a ready lane continues at once: its pixel's remaining bounces are the critical path)
         const bool batch = ready_m != 0u && (__popc(ready_m) >= (GI ? CRT_P_SHADE_TRIGGER_GI : CRT_P_SHADE_TRIGGER) || walking_m == 0u ||
                                              patience >= (exhausted && !GI ? 1 : (GI ? CRT_P_PATIENCE_GI : CRT_P_PATIENCE)));
-        if (batch || __any_sync(full, at_once)) {
+        if (batch || any_at_once) {
             patience = batch ? 0 : patience;
             if (ready && (batch || at_once)) {
                 int act = 0; // 0: consume the finished query, 1: shade_ray(ray, depth) entry, 2: return c to the callers
